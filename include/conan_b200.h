@@ -1,0 +1,174 @@
+/*
+ * conan_b200.h -- C ABI of the B200-native CONAN trajectory contact path.
+ *
+ * The reference (HITS-MBM/conan) has no FFI: its hot path is Python that shells out to
+ * `gmx mdmat` and then loops over the parsed text.  Every entry point below names the
+ * reference code (file:line under the reference tree) whose work it takes over; the host
+ * Python in conan_b200/ calls these through ctypes and is the only intended caller.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; pointers named d_* are DEVICE pointers, h_* / unnamed
+ *     `const uint8_t* data` are HOST pointers.  All buffers are caller-owned.
+ *   - no entry point allocates device memory; scratch is passed in (sizes from the
+ *     *_workspace_bytes helpers).
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  Calls are
+ *     asynchronous with respect to the host unless stated otherwise.
+ *   - return value: 0 = CONAN_OK, negative = error; conan_last_error() gives a
+ *     thread-local message.  Nothing here prints or exits (the reference's print +
+ *     sys.exit() behaviour stays on the Python side).
+ *   - pair index p ("condensed" order):
+ *       symmetric : residues i<j of nres, p = i*nres - i*(i+1)/2 + (j-i-1)   (P = nres(nres-1)/2)
+ *       block     : x in [0,xres), y in [0,yres), p = x*yres + y            (P = xres*yres)
+ *   - a level stack is uint16 [nf][stride], frame-major with a row pitch stride >= P (elements):
+ *     levels[f*stride + p] is the xpm level index gmx mdmat would have written for that
+ *     residue pair in that frame.  Columns P..stride-1 are padding and never read as data.
+ *   - nlevels is limited to 7744 = 88^2, the two-character xpm limit of gmx (docs/index.md:161).
+ */
+#ifndef CONAN_B200_H
+#define CONAN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CONAN_OK 0
+#define CONAN_ERR_ARG (-1)    /* bad argument (null pointer, negative size, ...) */
+#define CONAN_ERR_CUDA (-2)   /* a CUDA runtime / driver call failed */
+#define CONAN_ERR_FORMAT (-3) /* malformed trajectory data */
+#define CONAN_ERR_SIZE (-4)   /* problem exceeds a documented limit / workspace too small */
+
+/* Library version (major*10000 + minor*100 + patch). */
+int conan_version(void);
+/* Thread-local text of the last error returned on this thread ("" if none). */
+const char* conan_last_error(void);
+
+/* ------------------------------------------------------------------------------------ */
+/* Host side: .xtc trajectory reading.  Replaces the trajectory reading `gmx mdmat -f`    */
+/* does for conan.py:1437-1453 (mdmat_run) including its -b/-e/-dt frame filter, which    */
+/* the host applies to the times returned here.                                          */
+/* ------------------------------------------------------------------------------------ */
+
+/* Scan an in-memory .xtc.  On return *nframes / *natoms are set.  If `offsets` is non-NULL
+ * it receives min(cap, nframes) entries of: byte offset, step, time (ps), box (9 floats,
+ * row-major box vectors, nm).  Call once with cap = 0 to size the arrays. */
+int conan_xtc_index(const uint8_t* data, size_t nbytes, int64_t cap, int64_t* offsets,
+                    int32_t* steps, float* times, float* boxes, int64_t* nframes,
+                    int32_t* natoms);
+
+/* Decode `nsel_frames` frames (frame_ids index into `offsets`) on `nthreads` host threads.
+ * atom_sel (nsel entries, may be NULL = all atoms) picks the index group while decoding, so
+ * xyz_out is [nsel_frames][nsel][3] float32 nm -- the array that is copied to the GPU.
+ * xyz_out may be pinned host memory. */
+int conan_xtc_decode(const uint8_t* data, size_t nbytes, const int64_t* offsets,
+                     const int64_t* frame_ids, int64_t nsel_frames, int32_t natoms,
+                     const int32_t* atom_sel, int32_t nsel, float* xyz_out, int32_t nthreads);
+
+/* Write frames as a valid (uncompressed-run) .xtc into `out` (capacity cap bytes); *nbytes gets
+ * the size needed/used.  Used to materialise synthetic trajectories as real trajectory files. */
+int conan_xtc_encode(const float* xyz, const float* boxes, const int32_t* steps,
+                     const float* times, int64_t nframes, int32_t natoms, float precision,
+                     uint8_t* out, size_t cap, size_t* nbytes);
+
+/* ------------------------------------------------------------------------------------ */
+/* Stage 1: per-frame residue-residue minimum-distance matrix, quantised to xpm levels.  */
+/* Replaces `gmx mdmat -frames` as invoked by conan.py:1437-1453 (:1783-1784) and the    */
+/* text parse of its output, conan.py:455-567 (read_index / read_next_time / read_frame). */
+/* ------------------------------------------------------------------------------------ */
+
+/* Scratch bytes conan_mdmat_frames needs for nf frames (0 on bad arguments).  max_res_atoms
+ * = the largest number of atoms in one residue. */
+size_t conan_mdmat_workspace_bytes(int64_t nf, int32_t natoms, int32_t nres, int32_t max_res_atoms);
+
+/*
+ * d_xyz       [nf][natoms][3] float32 nm: the index group's atoms only, in trajectory order.
+ * d_box       [nf][9] float32 or NULL.  Used only when pbc = 1 (rectangular minimum image with
+ *             the box diagonal, as gmx pbc_dx does for rectangular boxes).
+ * h_res_start [nres+1] HOST array: atoms res_start[r] .. res_start[r+1]-1 form residue r (gmx
+ *             mdmat starts a new residue whenever the atom's residue index changes).
+ * symmetric=1: pairs i<j over all nres residues (x0,xres,y0,yres ignored).
+ * symmetric=0: block of residues [x0,x0+xres) x [y0,y0+yres) (the START_X/NRES_X/START_Y/NRES_Y
+ *             selection of conan.py:541-551).
+ * trunc, nlevels: gmx mdmat -t / -nlevels.  level = rint(r*(nlevels-1)/trunc) clamped to
+ *             [0, nlevels-1], r = float32 min over atom pairs, truncated at trunc.
+ * d_levels    [nf][levels_stride] uint16 out (columns >= P untouched).
+ * d_n_boundary (may be NULL) is incremented by the number of (frame, pair) results that lie
+ *             within 2 ulp of a level boundary (those may differ from gmx by one level).
+ * d_work      scratch of at least conan_mdmat_workspace_bytes(...) bytes.
+ */
+int conan_mdmat_frames(const float* d_xyz, const float* d_box, int64_t nf, int32_t natoms,
+                       const int32_t* h_res_start, int32_t nres, int32_t symmetric, int32_t x0,
+                       int32_t xres, int32_t y0, int32_t yres, float trunc, int32_t nlevels,
+                       int32_t pbc, uint16_t* d_levels, int64_t levels_stride,
+                       unsigned long long* d_n_boundary, void* d_work, size_t work_bytes,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------ */
+/* Stage 2: streaming per-pair statistics over a level stack.  Replaces the per-frame     */
+/* loop of read_process_frames, conan.py:782-874, with update_aggregate :599-611,         */
+/* update_interaction :24-45, the native / non-native counts :841-854 and rmsd_frame      */
+/* :1414-1432 (called from plot_frames :643-644).                                         */
+/* ------------------------------------------------------------------------------------ */
+
+/* Per-pair results; every array has P entries and is written, not accumulated. */
+typedef struct conan_pair_stats_out {
+    int64_t* d_sum_k;    /* sum over frames of the level index            (-> sum r,  :601) */
+    int64_t* d_sum_k2;   /* sum of squared level indices                  (-> sum r^2, :602) */
+    int32_t* d_n_int;    /* frames with the interaction on                (:605) */
+    int32_t* d_n_enc;    /* off -> on transitions                         (:607-610) */
+    int32_t* d_first_f;  /* first frame with the interaction on, -1 never (:608-609) */
+    int32_t* d_last_f;   /* last frame with the interaction on, -1 never  (:606) */
+    uint8_t* d_status;   /* status after the last frame                   (:611) */
+    uint16_t* d_kmin;    /* smallest level seen (pair is in pairs_list iff kmin < nlevels-1, :528-539) */
+    uint16_t* d_kmax;    /* largest level seen (kmin != kmax is the len(set(rvec)) > 1 test, :1902) */
+    uint8_t* d_decided;  /* 1 if some frame of this call was outside the hysteresis buffer */
+} conan_pair_stats_out;
+
+/* Per-frame results; nf entries each, frame numbering local to the call. */
+typedef struct conan_frame_stats_out {
+    int32_t* d_native;     /* pairs on in this frame that were on in global frame 0 (:852) */
+    int32_t* d_nonnative;  /* pairs on in this frame that were not              (:853) */
+    int64_t* d_ssd_prev;   /* sum over pairs (k_f - k_{f-1})^2 (rmsd_frame vs previous, :644) */
+    int64_t* d_ssd_first;  /* sum over pairs (k_f - k_0)^2     (rmsd_frame vs first,    :643) */
+} conan_frame_stats_out;
+
+/* Scratch bytes for conan_pair_stats (0 on bad arguments). */
+size_t conan_pair_stats_workspace_bytes(int64_t nf, int64_t P);
+
+/*
+ * d_levels  [nf][levels_stride] uint16, 8-byte aligned, levels_stride a multiple of 4.
+ *           frame0 = global index of the first frame of this call (frame numbers written to
+ *           first_f/last_f are global).
+ * lo_cnt / hi_first: TRUNC_INTER / TRUNC_INTER_HIGH in level space: r < trunc_inter <=> k < lo_cnt,
+ *           r > trunc_inter_high <=> k >= hi_first.  equal_cut = 1 selects the
+ *           `trunc_inter == trunc_inter_high` branch of update_interaction (:29-30).
+ * d_first_row [P] levels of GLOBAL frame 0 (defines "native" and the rmsd-to-first reference);
+ *           NULL = row 0 of d_levels.
+ * d_prev_row  [P] levels of the frame preceding this call's first frame; NULL = none (the
+ *           first frame then gets ssd_prev 0, as the reference's first frame writes no line).
+ * d_status_in [P] interaction status entering this call (frame shards after the first);
+ *           NULL = all off.
+ * Work is split into frame chunks x pair tiles inside; chunk records live in d_work.
+ */
+int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                     int64_t frame0, int32_t nlevels, int32_t lo_cnt, int32_t hi_first,
+                     int32_t equal_cut,
+                     const uint16_t* d_first_row, const uint16_t* d_prev_row,
+                     const uint8_t* d_status_in, const conan_pair_stats_out* out,
+                     const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
+                     void* stream);
+
+/* ------------------------------------------------------------------------------------ */
+/* Measurement helpers (bench.py only).                                                  */
+/* ------------------------------------------------------------------------------------ */
+
+/* Runs a dependent-FMA kernel on every SM and returns the achieved FP32 TFLOP/s
+ * (2 flops per FMA) in *tflops; used as the roofline denominator of stage 1. */
+int conan_measure_fp32_peak(double* tflops, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CONAN_B200_H */

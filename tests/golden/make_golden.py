@@ -1,0 +1,157 @@
+#!/usr/bin/env python3
+"""Generates the committed fixtures in tests/golden/ from the reference tree.
+
+Run HERE (where /root/reference exists):  python tests/golden/make_golden.py
+Nothing under tests/ reads /root/reference at test time; the GPU box has no reference tree.
+
+Fixtures written
+  sample.xtc            copy of the reference's 11-frame test trajectory (input data, 17 KB)
+  peptide.gro           topology of its 399 atoms, extracted from test/md.tpr, frame-0 coordinates
+  ref_goldens.npz       the reference's own golden outputs (test/*/correct_output) parsed to arrays,
+                        plus the 11 x 28 x 28 golden level matrices of test 1 and the 14 x 14 of test 8
+  case_*.npz            inputs and outputs of the UNMODIFIED reference run here (oracle/ref_runner.py)
+                        on synthetic level stacks that exercise hysteresis, observables, PCA,
+                        frame clustering and the asymmetric mode
+"""
+import os
+import shutil
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from conan_b200 import topology, xpm  # noqa: E402
+from conan_b200.xtc import XtcFile  # noqa: E402
+from oracle import ref_runner  # noqa: E402
+
+REF = "/root/reference"
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def parse_tree(root):
+    """Every .dat/.txt under root -> {relative path: float array} (np.loadtxt semantics)."""
+    res = {}
+    for dp, _, files in os.walk(root):
+        for fn in sorted(files):
+            if not (fn.endswith(".dat") or fn.endswith(".txt")):
+                continue
+            p = os.path.join(dp, fn)
+            try:
+                arr = np.loadtxt(p)
+            except Exception:
+                continue
+            res[os.path.relpath(p, root)] = arr
+    return res
+
+
+def reference_goldens():
+    out = {}
+    for test in ("1_ReadWrite", "2_Pearson", "3_ClusterTraj", "6_PCA", "8_Asymmetric"):
+        tree = parse_tree(os.path.join(REF, "test", test, "correct_output"))
+        for k, v in tree.items():
+            if k.startswith("matrices/"):
+                continue
+            out["%s/%s" % (test, k)] = v
+    lv = []
+    for f in range(11):
+        g = np.loadtxt(os.path.join(REF, "test/1_ReadWrite/correct_output/matrices/%05d.dat" % f))
+        lv.append(np.rint(g[:, 2] * 1000).astype(np.uint16).reshape(28, 28))
+    out["levels_sym"] = np.stack(lv)
+    lv = []
+    for f in range(11):
+        g = np.loadtxt(os.path.join(REF, "test/8_Asymmetric/correct_output/matrices/%05d.dat" % f))
+        lv.append(np.rint(g[:, 2] * 1000).astype(np.uint16).reshape(14, 14))
+    out["levels_asym"] = np.stack(lv)
+    out["observable"] = np.loadtxt(os.path.join(REF, "test/2_Pearson/observable.dat"), skiprows=2)
+    np.savez_compressed(os.path.join(OUT, "ref_goldens.npz"), **out)
+    print("ref_goldens.npz:", len(out), "arrays")
+
+
+def peptide_fixture():
+    shutil.copyfile(os.path.join(REF, "test/sample.xtc"), os.path.join(OUT, "sample.xtc"))
+    top = topology.read_tpr(os.path.join(REF, "test/md.tpr"))
+    x = XtcFile(os.path.join(OUT, "sample.xtc"))
+    xyz0 = x.decode(frame_ids=[0])[0]
+    box = x.boxes[0].diagonal()
+    topology.write_gro(os.path.join(OUT, "peptide.gro"), top, xyz0, box, "ACE-(33..58)-NME peptide of the CONAN tests")
+    print("peptide.gro:", top.natoms, "atoms")
+
+
+def synthetic_levels(seed, nf, nres, nlevels, lo, hi):
+    """Random-walk distances that cross the interaction cut-offs often; some pairs never in range."""
+    rng = np.random.default_rng(seed)
+    iu = np.triu_indices(nres, 1)
+    P = len(iu[0])
+    base = rng.uniform(0.15, 1.3, size=P)
+    walk = np.cumsum(rng.normal(0, 0.06, size=(nf, P)), axis=0)
+    r = np.clip(base + walk - walk.mean(axis=0), 0.0, 1.0)
+    r[:, rng.random(P) < 0.15] = 1.0           # pairs never within the truncation distance
+    far = rng.random(P) < 0.2                   # pairs that appear late
+    r[: nf // 3, far] = 1.0
+    lv = np.rint(r * (nlevels - 1)).astype(np.uint16)
+    full = np.zeros((nf, nres, nres), np.uint16)
+    full[:, iu[0], iu[1]] = lv
+    full[:, iu[1], iu[0]] = lv
+    return full
+
+
+def run_case(name, full, times, trunc, nlevels, keywords, obs=None):
+    work = tempfile.mkdtemp(prefix="conan_golden_")
+    with open(os.path.join(work, "dmf.xpm"), "w") as f:
+        xpm.write_xpm(f, full, times, trunc, nlevels)
+    text = "RUN_MDMAT no\nTRUNC %g\nNLEVEL %d\nMAKE_MOVIE no\n" % (trunc, nlevels) + keywords
+    if obs is not None:
+        with open(os.path.join(work, "obs.dat"), "w") as f:
+            f.write("%d\n" % obs.shape[1])
+            for k in range(obs.shape[1]):
+                f.write("observable %d\n" % k)
+            for t, row in zip(times, obs):
+                f.write("%d %s\n" % (t, " ".join("%.6f" % v for v in row)))
+        text += "PEARSON_OBS obs.dat\n"
+    g = ref_runner.run_reference(work, text)
+    out = {"in/levels_full": full, "in/times": np.asarray(times, np.float64), "in/trunc": np.float64(trunc),
+           "in/nlevels": np.int64(nlevels), "in/keywords": np.array(text)}
+    if obs is not None:
+        out["in/obs"] = obs
+    for k, v in parse_tree(work).items():
+        if k.startswith("input/") or k == "ref.inp" or k == "obs.dat":
+            continue
+        out["file/" + k] = v
+    out["ret/vectors"] = np.asarray(g["vectors"])
+    out["ret/pairs_list"] = np.asarray(g["pairs_list"], dtype=np.int64)
+    out["ret/time_vec"] = np.asarray(g["time_vec"], dtype=np.float64)
+    out["ret/trunc_inter"] = np.float64(g["trunc_inter"])
+    out["ret/trunc_inter_high"] = np.float64(g["trunc_inter_high"])
+    np.savez_compressed(os.path.join(OUT, "case_%s.npz" % name), **out)
+    shutil.rmtree(work)
+    print("case_%s.npz:" % name, len(out), "arrays;", "pairs", len(g["pairs_list"]))
+
+
+def main():
+    if not ref_runner.available():
+        sys.exit("needs /root/reference")
+    peptide_fixture()
+    reference_goldens()
+    nf, nres, nl = 48, 12, 101
+    times = np.arange(nf) * 100
+    full = synthetic_levels(11, nf, nres, nl, 0.5, 0.6)
+    rng = np.random.default_rng(5)
+    obs = np.stack([np.linspace(0, 1, nf) + rng.normal(0, 0.2, nf), rng.normal(0, 1, nf)], axis=1)
+    run_case("hyst", full, times, 1.0, nl,
+             "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nPEARSON_TIME yes\nPEARSON_INTER yes\nPCA_MAKE 3\n"
+             "K_TRAJ_CLUSTERS 2-3\nDR_MODE both\n", obs)
+    run_case("equalcut", full, times, 1.0, nl, "TRUNC_INTER 0.45\nMATRICES no\nPEARSON_TIME yes\n")
+    run_case("default", full[:20], times[:20], 1.0, nl, "MATRICES no\n")
+    run_case("asym", full, times, 1.0, nl,
+             "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nSTART_X 1\nNRES_X 5\nNTERM_X 1\nSTART_Y 6\nNRES_Y 7\nNTERM_Y 6\n"
+             "MATRICES no\nPEARSON_TIME yes\nK_TRAJ_CLUSTERS 2\n")
+    # finer legend: 1001 levels, trunc 1.5 (dx = 0.0015, not a multiple of 1e-4)
+    full2 = synthetic_levels(12, 30, 9, 1001, 0.5, 0.6)
+    run_case("fine", full2, np.arange(30) * 500 + 1000, 1.5, 1001,
+             "TRUNC_INTER 0.6\nTRUNC_INTER_HIGH 0.8\nMATRICES no\nPEARSON_TIME yes\nPCA_MAKE 2\n")
+
+
+if __name__ == "__main__":
+    main()

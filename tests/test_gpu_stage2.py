@@ -1,0 +1,104 @@
+"""Stage 2 parity on the GPU: conan_pair_stats through the C-ABI vs the CPU oracle, bit-exact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+PAIR_KEYS = ("sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f", "status", "kmin", "kmax")
+FRAME_KEYS = ("native", "nonnative", "ssd_prev", "ssd_first")
+
+
+def _device_stack(levels):
+    import torch
+    from conan_b200.levels import padded_stride
+    nf, P = levels.shape
+    stride = padded_stride(P)
+    buf = np.full((nf, stride), 0xABCD, dtype=np.uint16)     # padding holds junk on purpose
+    buf[:, :P] = levels
+    return torch.from_numpy(buf.view(np.int16)).cuda().view(torch.uint16)
+
+
+def _random_walk_levels(rng, nf, P, nlevels):
+    base = rng.uniform(0.1, 1.2, size=P)
+    r = np.clip(base + np.cumsum(rng.normal(0, 0.05, size=(nf, P)), axis=0), 0, 1)
+    r[:, rng.random(P) < 0.1] = 1.0
+    return np.rint(r * (nlevels - 1)).astype(np.uint16)
+
+
+def _check(got, want, first_frame=0):
+    for k in PAIR_KEYS + FRAME_KEYS:
+        w = want[k]
+        if k in ("first_f", "last_f") and first_frame:
+            w = np.where(w >= 0, w + first_frame, w)
+        assert np.array_equal(got[k], w), k
+
+
+@pytest.mark.parametrize("nf,P,nlevels,lo,hi,equal", [
+    (200, 2850, 1001, 500, 601, 0),       # ubiquitin-sized, several frame chunks
+    (1000, 333, 1001, 500, 601, 0),       # few pairs, many chunks: carries dominate
+    (77, 5001, 101, 45, 45, 1),           # equal cut-offs, ragged sizes
+    (40, 4096 + 3, 7744, 3000, 5000, 0),  # maximum level count
+    (1, 10, 11, 5, 8, 0),                 # a single frame
+    (33, 1, 40, 39, 39, 1),               # a single pair, default cut-offs (0.999999*trunc)
+])
+def test_matches_oracle(lib, orc, nf, P, nlevels, lo, hi, equal):
+    from conan_b200 import stage2
+    rng = np.random.default_rng(nf * 7 + P)
+    levels = _random_walk_levels(rng, nf, P, nlevels)
+    want = orc.pair_stats(levels, lo, hi, equal)
+    got = stage2.pair_stats(_device_stack(levels), P, nlevels, lo, hi, equal).host()
+    _check(got, want)
+
+
+def test_buffer_only_series_keeps_entering_status(lib, orc):
+    """Pairs that sit inside the hysteresis buffer for whole chunks must inherit the carry."""
+    from conan_b200 import stage2
+    nf, P = 640, 64
+    levels = np.full((nf, P), 55, np.uint16)          # buffer is [50, 60]
+    levels[0, ::2] = 10                                # half the pairs start on, then stay buffered
+    levels[400, ::4] = 90                              # a quarter of those switch off late
+    levels[500, 1::4] = 20
+    want = orc.pair_stats(levels, 50, 61, 0)
+    got = stage2.pair_stats(_device_stack(levels), P, 101, 50, 61, 0).host()
+    _check(got, want)
+    assert got["n_int"][0] == 400 and got["n_enc"][0] == 1
+
+
+def test_frame_shards_compose(lib, orc):
+    """Two calls over consecutive frame ranges, the second fed the first's state, equal one call."""
+    import torch
+    from conan_b200 import stage2
+    rng = np.random.default_rng(5)
+    nf, P, cut = 300, 1500, 137
+    levels = _random_walk_levels(rng, nf, P, 1001)
+    want = orc.pair_stats(levels, 500, 601, 0)
+    d = _device_stack(levels)
+    a = stage2.pair_stats(d[:cut], P, 1001, 500, 601, 0)
+    b = stage2.pair_stats(d[cut:], P, 1001, 500, 601, 0, frame0=cut, first_row=d[0], prev_row=d[cut - 1],
+                          status_in=a.status)
+    ha, hb = a.host(), b.host()
+    assert np.array_equal(ha["sum_k"] + hb["sum_k"], want["sum_k"])
+    assert np.array_equal(ha["sum_k2"] + hb["sum_k2"], want["sum_k2"])
+    assert np.array_equal(ha["n_int"] + hb["n_int"], want["n_int"])
+    assert np.array_equal(ha["n_enc"] + hb["n_enc"], want["n_enc"])
+    assert np.array_equal(np.where(ha["first_f"] >= 0, ha["first_f"], hb["first_f"]), want["first_f"])
+    assert np.array_equal(np.maximum(ha["last_f"], hb["last_f"]), want["last_f"])
+    assert np.array_equal(hb["status"], want["status"])
+    assert np.array_equal(np.minimum(ha["kmin"], hb["kmin"]), want["kmin"])
+    for k in FRAME_KEYS:
+        assert np.array_equal(np.concatenate([ha[k], hb[k]]), want[k]), k
+
+
+def test_bad_arguments_are_errors(lib):
+    import torch
+    from conan_b200 import stage2
+    from conan_b200._lib import ConanError
+    d = torch.zeros((4, 64), dtype=torch.uint16, device="cuda")
+    with pytest.raises(ConanError):
+        stage2.pair_stats(d, 10, 8000, 5, 6, 0)              # too many levels
+    with pytest.raises(ConanError):
+        stage2.pair_stats(d, 10, 101, 60, 50, 0)             # high cut-off below low cut-off
+    with pytest.raises(ConanError):
+        stage2.pair_stats(d, 100, 101, 50, 60, 0)            # P larger than the row pitch
+    with pytest.raises(ConanError):
+        stage2.pair_stats(d.cpu(), 10, 101, 50, 60, 0)       # host tensor: no CPU path
