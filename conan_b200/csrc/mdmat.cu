@@ -24,6 +24,8 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 
 #include "common.h"
 
@@ -112,8 +114,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded wait: a TMA that never lands must not hang the GPU; trap instead.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    for (uint32_t spin = 0; spin < (1u << 26); spin++)
+    for (uint32_t spin = 0; spin < (1u << 24); spin++)
         if (mbar_try_wait(bar, parity)) return;
+    if ((threadIdx.x & 31) == 0)
+        printf("conan mdmat: TMA tile load never completed (block %d warp %d)\n", (int)blockIdx.x, (int)(threadIdx.x >> 5));
     __trap();
 }
 __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0,
@@ -140,10 +144,13 @@ struct MdmatParams {
     int nres, nres_pad, kpad;
     int symmetric;
     int x0, xres, y0, yres;  // block mode (symmetric: x0=y0=0, xres=yres=nres)
+    int tx0, ty0;            // first 64-aligned tile of the x / y residue range
     int ntx, nty, ntiles;    // tile grid
     float trunc, trunc2, invlevel;
     int maxlevel;
     int pbc;
+    int use_tma;             // 0: stage tiles with plain loads (debug aid, CONAN_MDMAT_NO_TMA=1)
+    const float* slots;      // [nf][3][kpad][nres_pad], for the plain-load path
 };
 
 __device__ __forceinline__ float min_image(float d, float L) {
@@ -217,10 +224,12 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
         tj = t - ti * prm.nty;
     }
     const bool diag = prm.symmetric && ti == tj;
-    const int gi0 = prm.x0 + ti * kTile;   // first residue (index-group numbering) of the row tile
-    const int gj0 = prm.y0 + tj * kTile;
-    const int i_end = prm.symmetric ? prm.nres : prm.x0 + prm.xres;   // exclusive residue bounds
-    const int j_end = prm.symmetric ? prm.nres : prm.y0 + prm.yres;
+    // Tiles are aligned to multiples of kTile in the index group's residue numbering, so TMA
+    // coordinates are always tile-aligned and inside the padded tensor.
+    const int gi0 = (prm.tx0 + ti) * kTile;   // first residue of the row tile
+    const int gj0 = (prm.ty0 + tj) * kTile;
+    const int i_beg = prm.x0, i_end = prm.x0 + prm.xres;   // residue bounds [beg, end)
+    const int j_beg = prm.y0, j_end = prm.y0 + prm.yres;
 
     if (tid == 0) {
         mbar_init(bar, 1);
@@ -229,11 +238,20 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
         counters[1] = 0;
     }
     __syncthreads();
-    if (tid == 0) {
-        const uint32_t tile_bytes = 3u * (uint32_t)cstride * 4u;
-        mbar_expect_tx(bar, diag ? tile_bytes : 2u * tile_bytes);
-        tma_load_4d(atomsI, &tmap, bar, gi0, 0, 0, (int)f);
-        if (!diag) tma_load_4d(atomsJ, &tmap, bar, gj0, 0, 0, (int)f);
+    if (prm.use_tma) {
+        if (tid == 0) {
+            const uint32_t tile_bytes = 3u * (uint32_t)cstride * 4u;
+            mbar_expect_tx(bar, diag ? tile_bytes : 2u * tile_bytes);
+            tma_load_4d(atomsI, &tmap, bar, gi0, 0, 0, (int)f);
+            if (!diag) tma_load_4d(atomsJ, &tmap, bar, gj0, 0, 0, (int)f);
+        }
+    } else {
+        const float* src = prm.slots + (size_t)f * 3 * kpad * prm.nres_pad;
+        for (int idx = tid; idx < 3 * cstride; idx += kThreads) {
+            const int r = idx & (kTile - 1), ck = idx >> 6;   // ck = c*kpad + k
+            atomsI[idx] = gi0 + r < prm.nres_pad ? src[(size_t)ck * prm.nres_pad + gi0 + r] : 0.f;
+            if (!diag) atomsJ[idx] = gj0 + r < prm.nres_pad ? src[(size_t)ck * prm.nres_pad + gj0 + r] : 0.f;
+        }
     }
     if (tid < kTile) {
         const int g = gi0 + tid;
@@ -265,7 +283,8 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int j = lane + 32 * h;
-                const bool valid = gi < i_end && gj[h] < j_end && (!prm.symmetric || gj[h] > gi);
+                const bool valid = gi >= i_beg && gi < i_end && gj[h] >= j_beg && gj[h] < j_end &&
+                                   (!prm.symmetric || gj[h] > gi);
                 bool keep = false, general = false;
                 if (valid) {
                     float dx = si.x - sj[h].x, dy = si.y - sj[h].y, dz = si.z - sj[h].z;
@@ -294,7 +313,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
         }
     }
     __syncthreads();
-    mbar_wait(bar, 0);   // atom tiles have landed
+    if (prm.use_tma) mbar_wait(bar, 0);   // atom tiles have landed
 
     // ---- phase 2: exact minimum over atom pairs for the survivors --------------------------
     {
@@ -344,12 +363,13 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
         uint16_t* frame_out = prm.levels + (size_t)f * prm.stride;
         for (int i = warp; i < kTile; i += kThreads / 32) {
             const int gi = gi0 + i;
+            if (gi < i_beg) continue;
             if (gi >= i_end) break;
             // valid columns of this row: [jlo, jhi) in tile coordinates
-            int jlo = 0, jhi = min(kTile, j_end - gj0);
+            int jlo = max(0, j_beg - gj0), jhi = min(kTile, j_end - gj0);
             int64_t rowbase;   // element index of column gj0 in this row
             if (prm.symmetric) {
-                if (diag) jlo = i + 1;
+                if (diag) jlo = max(jlo, i + 1);
                 rowbase = (int64_t)gi * prm.nres - (int64_t)gi * (gi + 1) / 2 + (gj0 - gi - 1);
             } else {
                 rowbase = (int64_t)(gi - prm.x0) * prm.yres + (gj0 - prm.y0);
@@ -499,11 +519,18 @@ extern "C" int conan_mdmat_frames(const float* d_xyz, const float* d_box, int64_
     prm.P = symmetric ? (int64_t)nres * (nres - 1) / 2 : (int64_t)xres * yres;
     prm.nres = nres; prm.nres_pad = L.nres_pad; prm.kpad = L.kpad; prm.symmetric = symmetric ? 1 : 0;
     prm.x0 = x0; prm.xres = xres; prm.y0 = y0; prm.yres = yres;
-    prm.ntx = (xres + kTile - 1) / kTile;
-    prm.nty = (yres + kTile - 1) / kTile;
+    prm.tx0 = x0 / kTile;
+    prm.ty0 = y0 / kTile;
+    prm.ntx = (x0 + xres - 1) / kTile - prm.tx0 + 1;
+    prm.nty = (y0 + yres - 1) / kTile - prm.ty0 + 1;
     prm.ntiles = symmetric ? prm.ntx * (prm.ntx + 1) / 2 : prm.ntx * prm.nty;
     prm.trunc = trunc; prm.trunc2 = trunc * trunc; prm.invlevel = (float)(nlevels - 1) / trunc;
     prm.maxlevel = nlevels - 1; prm.pbc = pbc ? 1 : 0;
+    {
+        const char* e = getenv("CONAN_MDMAT_NO_TMA");
+        prm.use_tma = (e && e[0] == '1') ? 0 : 1;
+    }
+    prm.slots = d_slots;
     if (prm.P == 0) return CONAN_OK;
     if (levels_stride < prm.P)
         return conan::fail(CONAN_ERR_ARG, "conan_mdmat_frames: levels_stride=%lld < P=%lld", (long long)levels_stride, (long long)prm.P);
@@ -533,6 +560,7 @@ extern "C" int conan_mdmat_frames(const float* d_xyz, const float* d_box, int64_
         p2.box = d_box ? d_box + 9 * fb : nullptr;
         p2.levels = d_levels + (size_t)fb * prm.stride;
         p2.frame_base = 0;
+        p2.slots = d_slots + (size_t)fb * 3 * L.kpad * L.nres_pad;
         mdmat_tile_kernel<<<(unsigned)(nfl * prm.ntiles), kThreads, smem, stream>>>(tmap, p2);
         CONAN_CUDA_TRY(cudaGetLastError());
     }
