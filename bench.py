@@ -1,0 +1,395 @@
+#!/usr/bin/env python3
+"""Benchmark of the CONAN contact hot path: residue-pair-frames/s (min-dist + contact stats).
+
+    python bench.py --gpus N --steps K --warmup W            this implementation (CUDA, sm_100a)
+    python bench.py --impl reference --gpus N ...             the CPU restatement on the host cores
+
+A step is one pass of the hot path over one batch of synthetic input: stage 1 (coordinates ->
+uint16 level stack, conan_mdmat_frames) followed by stage 2 (streaming per-pair statistics,
+conan_pair_stats).  The workload is the per-GPU shard of BASELINE.json's configs[3]: a synthetic
+1000-residue system (8 heavy atoms per residue), 12 500 frames per GPU; at --gpus 8 this is the
+full 100 000-frame configuration, frames sharded across GPUs (weak scaling), per-pair moments
+merged with an NCCL all-reduce and the hysteresis state carried across shards.
+
+One JSON line is printed by rank 0 (see the repository's bench contract):
+  value      whole-job pair-frames/s with the coordinates already resident in HBM
+  e2e        same metric through the C-ABI with HOST (pinned) coordinates: H2D of every frame
+             batch and D2H of the per-pair / per-frame results inside the timed region
+  roofline   the dominant kernel (mdmat_tile_kernel), timed alone with CUDA events
+  cpu_baseline  the CPU oracle (a port: gmx is unavailable) on a bounded sample, one thread
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NRES = 1000
+ATOMS_PER_RES = 8
+FRAMES_PER_GPU = 12500
+TRUNC, NLEVELS = 1.0, 1001
+TRUNC_INTER, TRUNC_INTER_HIGH = 0.5, 0.6
+METRIC = "residue-pair-frames/s (min-dist + contact stats)"
+UNIT = "pair-frames/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU, help="frames per GPU")
+    ap.add_argument("--nres", type=int, default=NRES)
+    ap.add_argument("--batch", type=int, default=1250, help="frames per H2D batch of the e2e leg")
+    ap.add_argument("--cpu-frames", type=int, default=48, help="frames of the CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def thresholds():
+    from conan_b200.levels import legend_values, level_thresholds
+    return level_thresholds(legend_values(TRUNC, NLEVELS), TRUNC_INTER, TRUNC_INTER_HIGH)
+
+
+# --------------------------------------------------------------------------------------------
+# CPU legs (oracle port; the one place besides tests/smoke that may execute oracle/)
+# --------------------------------------------------------------------------------------------
+def cpu_pass(xyz, res_start, threads):
+    """Stage 1 + stage 2 of the CPU restatement on `threads` host threads; returns seconds."""
+    from oracle import oracle
+    oracle.load()
+    lo, hi, eq = thresholds()
+    nf, natoms = xyz.shape[0], xyz.shape[1]
+    sel = np.arange(natoms)
+    t0 = time.perf_counter()
+    if threads <= 1:
+        full = oracle.mdmat_levels(xyz, None, sel, res_start, TRUNC, NLEVELS, 0)
+    else:
+        parts = [None] * threads
+        bounds = np.linspace(0, nf, threads + 1).astype(int)
+
+        def work(i):
+            if bounds[i + 1] > bounds[i]:
+                parts[i] = oracle.mdmat_levels(xyz[bounds[i]:bounds[i + 1]], None, sel, res_start, TRUNC, NLEVELS, 0)
+
+        ts = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        full = np.concatenate([p for p in parts if p is not None])
+    lv = oracle.condensed(full)
+    if threads <= 1:
+        oracle.pair_stats(lv, lo, hi, eq)
+    else:
+        P = lv.shape[1]
+        bounds = np.linspace(0, P, threads + 1).astype(int)
+        ts = [threading.Thread(target=lambda a, b: oracle.pair_stats(np.ascontiguousarray(lv[:, a:b]), lo, hi, eq),
+                               args=(bounds[i], bounds[i + 1])) for i in range(threads) if bounds[i + 1] > bounds[i]]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """--impl reference: the CPU restatement with every host core, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from conan_b200 import synth
+    cores = os.cpu_count() or 1
+    threads = min(cores, 64)
+    nf = max(threads, min(args.cpu_frames * 4, 256))
+    xyz, res_start, _ = synth.make_trajectory(args.nres, nf, ATOMS_PER_RES, seed=4)
+    P = args.nres * (args.nres - 1) // 2
+    for _ in range(max(1, min(args.warmup, 1))):
+        cpu_pass(xyz, res_start, threads)
+    times = [cpu_pass(xyz, res_start, threads) for _ in range(max(1, min(args.steps, 3)))]
+    t = float(np.mean(times))
+    value = P * nf / t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(times), "warmup": 1, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32+u16", "data": "synthetic",
+        "config": {"workload": "C4 shard sample: %d residues x %d frames (of %d per GPU)" % (args.nres, nf, args.frames),
+                   "nres": args.nres, "atoms_per_res": ATOMS_PER_RES, "trunc": TRUNC, "nlevels": NLEVELS},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": "%d frames of the %d-residue system, frames split over %d threads; gmx mdmat and "
+                                   "conan.py themselves are unavailable on this box" % (nf, args.nres, threads)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------
+# GPU legs
+# --------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from conan_b200 import _lib, stage1, stage2, synth, sharded
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for --impl ours)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    nf, nres = args.frames, args.nres
+    # one long trajectory, each rank generating its own frame range statistics (independent seeds)
+    xyz, res_start, _ = synth.make_trajectory(nres, nf, ATOMS_PER_RES, seed=4 + rank)
+    geom = stage1.Geometry(res_start)
+    P = geom.P
+    lo, hi, eq = thresholds()
+
+    h_xyz = torch.from_numpy(xyz).pin_memory()
+    d_xyz = h_xyz.to(dev)
+    levels = torch.zeros((nf, geom.stride), dtype=torch.uint16, device=dev)
+    counters = torch.zeros(3, dtype=torch.int64, device=dev)
+    work1 = torch.empty(stage1.mdmat_workspace_bytes(nf, geom), dtype=torch.uint8, device=dev)
+    work2 = torch.empty(stage2.pair_stats_workspace_bytes(nf, P), dtype=torch.uint8, device=dev)
+    out = stage2.PairStats(nf, P, dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    launches = [0]
+
+    def step_resident():
+        stage1.mdmat_frames(d_xyz, None, geom, TRUNC, NLEVELS, False, levels, work1, counters)
+        launches[0] += 2
+        if world > 1:
+            sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
+            launches[0] += 5
+        else:
+            stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2)
+            launches[0] += 3
+
+    # ---- device-resident throughput --------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches[0] = 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    n_launch = launches[0]
+
+    # ---- kernel-level timings for the roofline (same stream, CUDA events) -------------------
+    def time_region(fn, reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev)
+        a.record(stream)
+        for _ in range(reps):
+            fn()
+        b.record(stream)
+        torch.cuda.synchronize(dev)
+        return a.elapsed_time(b) / reps
+
+    reps = max(2, min(args.steps, 5))
+    counters.zero_()
+    stage1.mdmat_frames(d_xyz, None, geom, TRUNC, NLEVELS, False, levels, work1, counters)
+    torch.cuda.synchronize(dev)
+    cnt = counters.cpu().numpy().astype(np.float64)
+    ms_prep = time_region(lambda: stage1.mdmat_frames(d_xyz, None, geom, TRUNC, NLEVELS, False, levels, work1, None, phases=1), reps)
+    ms_tile = time_region(lambda: stage1.mdmat_frames(d_xyz, None, geom, TRUNC, NLEVELS, False, levels, work1, None, phases=2), reps)
+    ms_stats = time_region(lambda: stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2), reps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end to end from host memory --------------------------------------------------------
+    batch = max(1, min(args.batch, nf))
+    nb = (nf + batch - 1) // batch
+    stage_buf = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(2)]
+    work_b = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
+    copy_stream = torch.cuda.Stream(dev)
+    host_out = {n: torch.empty(getattr(out, n).shape, dtype=getattr(out, n).dtype).pin_memory()
+                for n, _ in stage2.PairStats.PAIR_FIELDS + stage2.PairStats.FRAME_FIELDS}
+    d2h_bytes = sum(t.numel() * t.element_size() for t in host_out.values())
+    h2d_bytes = h_xyz.numel() * 4
+
+    def step_e2e():
+        copied = [torch.cuda.Event() for _ in range(nb)]
+        consumed = [torch.cuda.Event() for _ in range(nb)]
+        for b in range(nb):
+            b0, b1 = b * batch, min(nf, (b + 1) * batch)
+            with torch.cuda.stream(copy_stream):
+                if b >= 2:
+                    copy_stream.wait_event(consumed[b - 2])
+                stage_buf[b % 2][: b1 - b0].copy_(h_xyz[b0:b1], non_blocking=True)
+                copied[b].record(copy_stream)
+            stream.wait_event(copied[b])
+            stage1.mdmat_frames(stage_buf[b % 2][: b1 - b0], None, geom, TRUNC, NLEVELS, False, levels[b0:b1], work_b, None)
+            consumed[b].record(stream)
+        if world > 1:
+            sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
+        else:
+            stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2)
+        for n in host_out:
+            host_out[n].copy_(getattr(out, n), non_blocking=True)
+
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(stream)
+    for _ in range(args.steps):
+        step_e2e()
+    b.record(stream)
+    barrier()
+    ms_e2e = a.elapsed_time(b)
+
+    # ---- reduce over ranks -----------------------------------------------------------------
+    t = torch.tensor([ms, ms_e2e, ms_tile, ms_stats, ms_prep], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e, ms_tile, ms_stats, ms_prep = [float(v) for v in t.cpu()]
+
+    if rank == 0:
+        pk, pk_kind = peaks()
+        fp32_peak = ctypes.c_double()
+        _lib.check(lib.conan_measure_fp32_peak(ctypes.byref(fp32_peak), stream.cuda_stream))
+        units = float(P) * nf * world                      # pair-frames per step, whole job
+        value = units * args.steps / (ms * 1e-3)
+        e2e_value = units * args.steps / (ms_e2e * 1e-3)
+        # stage 1 algorithmic work per launch (one GPU): 8 flop per evaluated atom pair (3 sub,
+        # 3 mul, 2 add) for the residue pairs that survive pruning + 2 B written per pair-frame
+        flops = 8.0 * cnt[2]
+        tile_tflops = flops / (ms_tile * 1e-3) / 1e12
+        stats_gbs = 2.0 * P * nf / (ms_stats * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32+u16", "data": "synthetic",
+            "config": {
+                "workload": "C4 shard: %d residues x %d frames per GPU (BASELINE configs[3] = 8 such shards)" % (nres, nf),
+                "nres": nres, "atoms_per_res": ATOMS_PER_RES, "pairs": P, "frames_per_gpu": nf,
+                "trunc": TRUNC, "nlevels": NLEVELS, "trunc_inter": TRUNC_INTER, "trunc_inter_high": TRUNC_INTER_HIGH,
+                "sharding": "frames x%d" % world,
+                "l2": "inputs larger than L2 (%.1f GB coordinates, %.1f GB levels per GPU); no flush needed"
+                      % (h2d_bytes / 1e9, levels.numel() * 2 / 1e9),
+            },
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": n_launch,
+            "clocks": clocks,
+            "roofline": {
+                "kernel": "mdmat_tile_kernel", "bound": "fp32", "achieved": tile_tflops, "peak": fp32_peak.value,
+                "unit": "TFLOP/s", "frac": tile_tflops / fp32_peak.value if fp32_peak.value else None,
+                "traffic": None, "ms": ms_tile,
+                "peak_source": "FP32 FMA rate measured in this run (conan_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
+                "algorithmic": "8 flop x %.4g atom pairs (%.1f%% of residue pairs survive pruning)"
+                               % (cnt[2], 100.0 * cnt[1] / (float(P) * nf)),
+                "hbm_view": {"achieved": 2.0 * P * nf / (ms_tile * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                             "frac": 2.0 * P * nf / (ms_tile * 1e-3) / 1e9 / pk["hbm_gbs"], "peak_kind": pk_kind},
+            },
+            "roofline_stats": {"kernel": "pair_stats_kernel (+combine)", "bound": "hbm", "achieved": stats_gbs,
+                               "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": stats_gbs / pk["hbm_gbs"],
+                               "traffic": None, "ms": ms_stats, "peak_kind": pk_kind},
+            "stage_ms": {"prep_slots_kernel": ms_prep, "mdmat_tile_kernel": ms_tile, "pair_stats": ms_stats},
+            "boundary_results": int(cnt[0]),
+        }
+        if not args.no_cpu_baseline:
+            ncpu = max(4, args.cpu_frames)
+            t_cpu = cpu_pass(xyz[:ncpu], res_start, 1)
+            line["cpu_baseline"] = {
+                "value": float(P) * ncpu / t_cpu, "unit": UNIT, "cores": 1, "kind": "port",
+                "sample": "first %d frames of the same %d-residue shard (%.1f s of one host core; host has %d cores); "
+                          "gmx mdmat itself: unavailable on this box" % (ncpu, nres, t_cpu, os.cpu_count() or 0)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -51,6 +51,13 @@ SIGNATURES = {
     "conan_mdmat_frames": (ctypes.c_int, [c_void_p, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_i32,
                                           c_i32, c_i32, c_i32, c_i32, c_f32, c_i32, c_i32, c_void_p,
                                           c_i64, c_void_p, c_void_p, c_size, c_void_p]),
+    "conan_mdmat_frames_ex": (ctypes.c_int, [c_void_p, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_i32,
+                                             c_i32, c_i32, c_i32, c_i32, c_f32, c_i32, c_i32, c_void_p,
+                                             c_i64, c_void_p, c_void_p, c_size, c_void_p, c_i32]),
+    "conan_pair_stats_ex": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32,
+                                           c_i32, c_void_p, c_void_p, c_void_p,
+                                           ctypes.POINTER(PairStatsOut), ctypes.POINTER(FrameStatsOut),
+                                           c_void_p, c_size, c_void_p, c_i32]),
     "conan_pair_stats_workspace_bytes": (c_size, [c_i64, c_i64]),
     "conan_pair_stats": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32,
                                         c_i32, c_void_p, c_void_p, c_void_p,

@@ -138,7 +138,7 @@ struct MdmatParams {
     const float* box;        // [nf][9] or nullptr
     uint16_t* levels;        // [nf][stride]
     int64_t stride;          // elements between frames
-    unsigned long long* n_boundary;
+    unsigned long long* counters;   // [0] near-boundary results [1] un-pruned residue pairs [2] atom pairs evaluated
     int64_t P;
     int64_t frame_base;      // first frame of this launch
     int nres, nres_pad, kpad;
@@ -202,7 +202,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
     constexpr int kOutStride = kTile + 2;
     uint16_t* list = outT + kTile * kOutStride;                   // [kTile*kTile]
     uint64_t* bar = reinterpret_cast<uint64_t*>(list + kTile * kTile);
-    int* counters = reinterpret_cast<int*>(bar + 1);              // [0] survivors, [1] boundary hits
+    int* counters = reinterpret_cast<int*>(bar + 1);              // [0] survivors, [1] boundary hits, [2] atom pairs
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t blk = blockIdx.x;
@@ -236,6 +236,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
         fence_mbar_init();
         counters[0] = 0;
         counters[1] = 0;
+        counters[2] = 0;
     }
     __syncthreads();
     if (prm.use_tma) {
@@ -319,7 +320,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
     {
         const int nsurv = counters[0];
         const float* aJbase = diag ? atomsI : atomsJ;
-        int near = 0;
+        int near = 0, evals = 0;
         for (int s = tid; s < nsurv; s += kThreads) {
             const int e = list[s];
             const int i = e & 63, j = (e >> 6) & 63;
@@ -327,6 +328,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
             const float* aI = atomsI + i;
             const float* aJ = aJbase + j;
             float m = prm.trunc2;
+            evals += ci * cj;
             if (!(e & 0x1000)) {
                 int a0 = 0;
                 while (ci - a0 > 4) { m = chunk_min<8>(aI, aJ, cstride, a0, cj, m); a0 += 8; }
@@ -351,9 +353,11 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
             const float frac = fabsf(tq - rintf(tq));
             near += (fabsf(frac - 0.5f) <= tq * 2.4e-7f) ? 1 : 0;
         }
-        if (prm.n_boundary) {
+        if (prm.counters) {
             near = __reduce_add_sync(0xffffffffu, near);
+            evals = __reduce_add_sync(0xffffffffu, evals);
             if (lane == 0 && near) atomicAdd(&counters[1], near);
+            if (lane == 0 && evals) atomicAdd(&counters[2], evals);
         }
     }
     __syncthreads();
@@ -391,8 +395,11 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
             }
             if (((jhi - j) & 1) && lane == 0) dst[jhi - 1] = src[jhi - 1];
         }
-        if (tid == 0 && prm.n_boundary && counters[1])
-            atomicAdd(prm.n_boundary, (unsigned long long)counters[1]);
+        if (tid == 0 && prm.counters) {
+            if (counters[1]) atomicAdd(&prm.counters[0], (unsigned long long)counters[1]);
+            if (counters[0]) atomicAdd(&prm.counters[1], (unsigned long long)counters[0]);
+            if (counters[2]) atomicAdd(&prm.counters[2], (unsigned long long)counters[2]);
+        }
     }
 }
 
@@ -426,7 +433,7 @@ size_t mdmat_smem_bytes(int kpad) {
     s += 2 * kTile * sizeof(int);                         // counts
     s += (size_t)kTile * (kTile + 2) * sizeof(uint16_t);  // output tile
     s += (size_t)kTile * kTile * sizeof(uint16_t);        // survivor list
-    s += 8 + 2 * sizeof(int);                             // mbarrier + counters
+    s += 8 + 4 * sizeof(int);                             // mbarrier + counters
     return (s + 15) & ~(size_t)15;
 }
 
@@ -459,8 +466,18 @@ extern "C" int conan_mdmat_frames(const float* d_xyz, const float* d_box, int64_
                                   const int32_t* h_res_start, int32_t nres, int32_t symmetric, int32_t x0,
                                   int32_t xres, int32_t y0, int32_t yres, float trunc, int32_t nlevels,
                                   int32_t pbc, uint16_t* d_levels, int64_t levels_stride,
-                                  unsigned long long* d_n_boundary, void* d_work, size_t work_bytes,
+                                  unsigned long long* d_counters, void* d_work, size_t work_bytes,
                                   void* stream_) {
+    return conan_mdmat_frames_ex(d_xyz, d_box, nf, natoms, h_res_start, nres, symmetric, x0, xres, y0, yres, trunc,
+                                 nlevels, pbc, d_levels, levels_stride, d_counters, d_work, work_bytes, stream_, 3);
+}
+
+extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int64_t nf, int32_t natoms,
+                                     const int32_t* h_res_start, int32_t nres, int32_t symmetric, int32_t x0,
+                                     int32_t xres, int32_t y0, int32_t yres, float trunc, int32_t nlevels,
+                                     int32_t pbc, uint16_t* d_levels, int64_t levels_stride,
+                                     unsigned long long* d_counters, void* d_work, size_t work_bytes,
+                                     void* stream_, int32_t phases) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (!d_xyz || !h_res_start || !d_levels || !d_work)
         return conan::fail(CONAN_ERR_ARG, "conan_mdmat_frames: null pointer argument");
@@ -498,15 +515,16 @@ extern "C" int conan_mdmat_frames(const float* d_xyz, const float* d_box, int64_
     float4* d_sph = reinterpret_cast<float4*>(w + L.off_sph);
     float* d_slots = reinterpret_cast<float*>(w + L.off_slots);
 
-    CONAN_CUDA_TRY(cudaMemcpyAsync(d_res_start, h_res_start, sizeof(int) * (size_t)(nres + 1),
-                                   cudaMemcpyHostToDevice, stream));
-    {
+    if (phases & 1) {
+        CONAN_CUDA_TRY(cudaMemcpyAsync(d_res_start, h_res_start, sizeof(int) * (size_t)(nres + 1),
+                                       cudaMemcpyHostToDevice, stream));
         const int64_t total = nf * L.nres_pad;
         const int threads = 128;
         prep_slots_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, stream>>>(
             d_xyz, d_res_start, nf, natoms, nres, L.nres_pad, L.kpad, d_slots, d_sph, d_cnt);
         CONAN_CUDA_TRY(cudaGetLastError());
     }
+    if (!(phases & 2)) return CONAN_OK;
 
     EncodeTiledFn encode = get_encode_fn();
     if (!encode) return conan::fail(CONAN_ERR_CUDA, "conan_mdmat_frames: cuTensorMapEncodeTiled unavailable");
@@ -515,7 +533,7 @@ extern "C" int conan_mdmat_frames(const float* d_xyz, const float* d_box, int64_
     CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 
     MdmatParams prm;
-    prm.sph = d_sph; prm.cnt = d_cnt; prm.box = d_box; prm.levels = d_levels; prm.n_boundary = d_n_boundary;
+    prm.sph = d_sph; prm.cnt = d_cnt; prm.box = d_box; prm.levels = d_levels; prm.counters = d_counters;
     prm.P = symmetric ? (int64_t)nres * (nres - 1) / 2 : (int64_t)xres * yres;
     prm.nres = nres; prm.nres_pad = L.nres_pad; prm.kpad = L.kpad; prm.symmetric = symmetric ? 1 : 0;
     prm.x0 = x0; prm.xres = xres; prm.y0 = y0; prm.yres = yres;

@@ -378,6 +378,17 @@ extern "C" int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride,
                                 const uint8_t* d_status_in, const conan_pair_stats_out* out,
                                 const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
                                 void* stream_) {
+    return conan_pair_stats_ex(d_levels, levels_stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
+                               d_first_row, d_prev_row, d_status_in, out, fout, d_work, work_bytes, stream_, 0);
+}
+
+extern "C" int conan_pair_stats_ex(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                                   int64_t frame0, int32_t nlevels, int32_t lo_cnt, int32_t hi_first,
+                                   int32_t equal_cut,
+                                   const uint16_t* d_first_row, const uint16_t* d_prev_row,
+                                   const uint8_t* d_status_in, const conan_pair_stats_out* out,
+                                   const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
+                                   void* stream_, int32_t recombine) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (!d_levels || !out || !fout || !d_work)
         return conan::fail(CONAN_ERR_ARG, "conan_pair_stats: null pointer argument");
@@ -425,10 +436,12 @@ extern "C" int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride,
     int* diff_n = reinterpret_cast<int*>(w + pl.off_diff_n);
     int* diff_nn = reinterpret_cast<int*>(w + pl.off_diff_nn);
 
-    CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_native, 0, sizeof(int) * (size_t)nf, stream));
-    CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_nonnative, 0, sizeof(int) * (size_t)nf, stream));
-    CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_ssd_prev, 0, sizeof(int64_t) * (size_t)nf, stream));
-    CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_ssd_first, 0, sizeof(int64_t) * (size_t)nf, stream));
+    if (!recombine) {
+        CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_native, 0, sizeof(int) * (size_t)nf, stream));
+        CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_nonnative, 0, sizeof(int) * (size_t)nf, stream));
+        CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_ssd_prev, 0, sizeof(int64_t) * (size_t)nf, stream));
+        CONAN_CUDA_TRY(cudaMemsetAsync(fout->d_ssd_first, 0, sizeof(int64_t) * (size_t)nf, stream));
+    }
     CONAN_CUDA_TRY(cudaMemsetAsync(diff_n, 0, sizeof(int) * (size_t)(nf + 1), stream));
     CONAN_CUDA_TRY(cudaMemsetAsync(diff_nn, 0, sizeof(int) * (size_t)(nf + 1), stream));
 
@@ -443,9 +456,11 @@ extern "C" int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride,
     sp.rec = rec;
     const int64_t tiles = (P + kPairsPerCta - 1) / kPairsPerCta;
     if (tiles > 2147483647ll) return conan::fail(CONAN_ERR_SIZE, "conan_pair_stats: too many pairs");
-    dim3 grid((unsigned)tiles, (unsigned)pl.nchunks);
-    pair_stats_kernel<<<grid, kThreads, 0, stream>>>(sp);
-    CONAN_CUDA_TRY(cudaGetLastError());
+    if (!recombine) {
+        dim3 grid((unsigned)tiles, (unsigned)pl.nchunks);
+        pair_stats_kernel<<<grid, kThreads, 0, stream>>>(sp);
+        CONAN_CUDA_TRY(cudaGetLastError());
+    }
 
     CombineParams cp;
     cp.rec = rec; cp.nchunks = pl.nchunks; cp.P = P; cp.nf = nf; cp.frame0 = frame0; cp.chunk_len = pl.chunk_len;

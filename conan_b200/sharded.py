@@ -1,0 +1,96 @@
+"""Frame shards across GPUs: what is exchanged so that stage 2 equals one long single-GPU run.
+
+Frames are independent for stage 1, so every rank computes the level stack of its own contiguous
+frame range.  Stage 2 needs three small exchanges:
+  1. the level row of GLOBAL frame 0 (defines "native" contacts and the rmsd-to-first reference)
+     and the last row of the preceding shard (rmsd-to-previous of the shard's first frame);
+  2. the interaction status entering each shard: every rank first runs under "enter off" and
+     publishes, per pair, whether its shard saw a decisive frame and the status it leaves with;
+     an exclusive scan over ranks gives the true entering status, and the chunk records are
+     folded once more under it (conan_pair_stats_ex recombine, no second pass over the stack);
+  3. the per-pair sums: all-reduce SUM of the integer moments and counts, MIN / MAX of the
+     first / last frame and level extremes.  Integer sums make the merge exact and
+     order-independent.
+The collectives are torch.distributed (NCCL over NVLink on the GPUs, gloo in the CPU tests).
+"""
+import torch
+import torch.distributed as dist
+
+_INT_MAX = 2 ** 31 - 1
+
+
+def _raw(t):
+    """Byte view for pure data movement (the collectives have no 16-bit unsigned type)."""
+    return t.contiguous().view(torch.uint8)
+
+
+def _reduce16(t, op, group):
+    """MIN / MAX of a 16-bit level tensor through int32 (levels are < 7744)."""
+    signed = t.view(torch.int16) if t.dtype == torch.uint16 else t
+    wide = signed.to(torch.int32)
+    dist.all_reduce(wide, op=op, group=group)
+    signed.copy_(wide.to(torch.int16))
+
+
+def exchange_rows(first_row_local, last_row_local, group=None):
+    """-> (row of global frame 0, last row of the preceding rank or None for rank 0)."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    first = _raw(first_row_local).clone()
+    dist.broadcast(first, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    mine = _raw(last_row_local)
+    lasts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(lasts, mine, group=group)
+    prev = lasts[rank - 1] if rank > 0 else None
+    back = lambda t: t.view(first_row_local.dtype)
+    return back(first), (None if prev is None else back(prev))
+
+
+def entering_status(decided, status_out, group=None):
+    """Exclusive scan of the shards' (decided, status) summaries -> status entering this rank."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dec = [torch.empty_like(decided) for _ in range(world)]
+    sta = [torch.empty_like(status_out) for _ in range(world)]
+    dist.all_gather(dec, decided.contiguous(), group=group)
+    dist.all_gather(sta, status_out.contiguous(), group=group)
+    s = torch.zeros_like(status_out)
+    for q in range(rank):
+        s = torch.where(dec[q] != 0, sta[q], s)
+    return s
+
+
+def merge_pair_stats(st, group=None):
+    """All-reduce the per-pair fields of `st` (an object with tensor attributes) in place."""
+    world = dist.get_world_size(group)
+    for name in ("sum_k", "sum_k2", "n_int", "n_enc"):
+        dist.all_reduce(getattr(st, name), op=dist.ReduceOp.SUM, group=group)
+    first = st.first_f
+    first.copy_(torch.where(first < 0, torch.full_like(first, _INT_MAX), first))
+    dist.all_reduce(first, op=dist.ReduceOp.MIN, group=group)
+    first.copy_(torch.where(first == _INT_MAX, torch.full_like(first, -1), first))
+    dist.all_reduce(st.last_f, op=dist.ReduceOp.MAX, group=group)
+    _reduce16(st.kmin, dist.ReduceOp.MIN, group)
+    _reduce16(st.kmax, dist.ReduceOp.MAX, group)
+    dist.all_reduce(st.decided, op=dist.ReduceOp.MAX, group=group)
+    # the status after the last frame is the last shard's
+    src = dist.get_global_rank(group, world - 1) if group is not None else world - 1
+    dist.broadcast(st.status, src=src, group=group)
+    return st
+
+
+def pair_stats_sharded(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0, out=None, work=None, group=None,
+                       local_pass=None):
+    """Stage 2 over this rank's frame shard, merged so that per-pair results equal a single run.
+
+    Per-frame results stay local to the rank (frames are disjoint).  `local_pass` exists for the
+    CPU tests: a callable with the signature of stage2.pair_stats."""
+    if local_pass is None:
+        from . import stage2
+        local_pass = stage2.pair_stats
+    first_row, prev_row = exchange_rows(levels[0], levels[-1], group)
+    st = local_pass(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=frame0, first_row=first_row,
+                    prev_row=prev_row, status_in=None, out=out, work=work)
+    s_in = entering_status(st.decided, st.status, group)
+    if dist.get_rank(group) > 0:
+        st = local_pass(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=frame0, first_row=first_row,
+                        prev_row=prev_row, status_in=s_in, out=st, work=getattr(st, "work", work), recombine=True)
+    return merge_pair_stats(st, group)

@@ -39,10 +39,12 @@ def mdmat_workspace_bytes(nf, geom):
     return n
 
 
-def mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, pbc, d_levels, d_work, d_n_boundary=None, stream=None):
+def mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, pbc, d_levels, d_work, d_counters=None, stream=None,
+                 phases=3):
     """Launch stage 1 for the frames in d_xyz ([nf, natoms, 3] float32, device) into d_levels.
 
-    d_levels is a uint16 (or int16-viewed) device tensor [nf, geom.stride]."""
+    d_levels is a uint16 device tensor [nf, geom.stride]; d_counters an int64[3] device tensor
+    (near-boundary results, un-pruned residue pairs, atom pairs evaluated) that is added to."""
     lib = _lib.load()
     if not d_xyz.is_cuda:
         raise _lib.ConanError(-1, "stage 1 needs device tensors: there is no CPU fallback")
@@ -52,11 +54,11 @@ def mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, pbc, d_levels, d_work, d_n_
     assert d_xyz.dtype == torch.float32 and d_xyz.is_contiguous() and d_xyz.shape[1] == geom.natoms
     assert d_levels.is_contiguous() and d_levels.shape[0] >= nf and d_levels.shape[1] == geom.stride
     s = stream if stream is not None else torch.cuda.current_stream(d_xyz.device)
-    _lib.check(lib.conan_mdmat_frames(
+    _lib.check(lib.conan_mdmat_frames_ex(
         d_xyz.data_ptr(), _ptr(d_box), nf, geom.natoms, geom.res_start.ctypes.data, geom.nres,
         1 if geom.symmetric else 0, geom.x0, geom.xres, geom.y0, geom.yres, float(trunc), int(nlevels),
-        1 if pbc else 0, d_levels.data_ptr(), geom.stride, _ptr(d_n_boundary), d_work.data_ptr(),
-        d_work.numel() * d_work.element_size(), s.cuda_stream))
+        1 if pbc else 0, d_levels.data_ptr(), geom.stride, _ptr(d_counters), d_work.data_ptr(),
+        d_work.numel() * d_work.element_size(), s.cuda_stream, phases))
     return d_levels
 
 
@@ -66,7 +68,7 @@ def compute_levels(xyz, boxes, geom, trunc, nlevels, pbc=False, device="cuda", b
     nf = xyz.shape[0]
     dev = torch.device(device)
     levels = out if out is not None else torch.zeros((nf, geom.stride), dtype=torch.uint16, device=dev)
-    nb = torch.zeros(1, dtype=torch.int64, device=dev)
+    nb = torch.zeros(3, dtype=torch.int64, device=dev)
     batch = max(1, min(batch, nf))
     work = torch.empty(mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
     for b0 in range(0, nf, batch):
@@ -77,4 +79,4 @@ def compute_levels(xyz, boxes, geom, trunc, nlevels, pbc=False, device="cuda", b
             d_box = torch.from_numpy(np.ascontiguousarray(boxes[b0:b1], dtype=np.float32).reshape(-1, 9)).to(dev)
         mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, pbc, levels[b0:b1], work, nb)
     torch.cuda.synchronize(dev)
-    return levels, int(nb.item())
+    return levels, int(nb[0].item())

@@ -47,7 +47,7 @@ def pair_stats_workspace_bytes(nf, P):
 
 
 def pair_stats(d_levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=0, first_row=None, prev_row=None,
-               status_in=None, out=None, work=None, stream=None):
+               status_in=None, out=None, work=None, stream=None, recombine=False):
     """Launch stage 2 on a device level stack [nf, stride] (uint16); returns PairStats (device)."""
     lib = _lib.load()
     if not d_levels.is_cuda:
@@ -62,8 +62,9 @@ def pair_stats(d_levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=0, firs
     fo = _lib.FrameStatsOut(*[getattr(out, n).data_ptr() for n, _ in PairStats.FRAME_FIELDS])
     s = stream if stream is not None else torch.cuda.current_stream(dev)
     ptr = lambda t: 0 if t is None else t.data_ptr()
-    _lib.check(lib.conan_pair_stats(d_levels.data_ptr(), stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
-                                    ptr(first_row), ptr(prev_row), ptr(status_in), ctypes.byref(po), ctypes.byref(fo),
-                                    work.data_ptr(), work.numel(), s.cuda_stream))
-    out._keepalive = (work, first_row, prev_row, status_in)
+    _lib.check(lib.conan_pair_stats_ex(d_levels.data_ptr(), stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
+                                       ptr(first_row), ptr(prev_row), ptr(status_in), ctypes.byref(po), ctypes.byref(fo),
+                                       work.data_ptr(), work.numel(), s.cuda_stream, 1 if recombine else 0))
+    out.work = work
+    out._keepalive = (first_row, prev_row, status_in)
     return out

@@ -94,16 +94,28 @@ size_t conan_mdmat_workspace_bytes(int64_t nf, int32_t natoms, int32_t nres, int
  * trunc, nlevels: gmx mdmat -t / -nlevels.  level = rint(r*(nlevels-1)/trunc) clamped to
  *             [0, nlevels-1], r = float32 min over atom pairs, truncated at trunc.
  * d_levels    [nf][levels_stride] uint16 out (columns >= P untouched).
- * d_n_boundary (may be NULL) is incremented by the number of (frame, pair) results that lie
- *             within 2 ulp of a level boundary (those may differ from gmx by one level).
+ * d_counters  (may be NULL) three device counters that are incremented, never reset:
+ *             [0] (frame, pair) results within 2 ulp of a level boundary (those may differ from
+ *                 gmx by one level), [1] residue pairs that survived bounding-sphere pruning,
+ *             [2] atom-pair distances evaluated for them.
  * d_work      scratch of at least conan_mdmat_workspace_bytes(...) bytes.
  */
 int conan_mdmat_frames(const float* d_xyz, const float* d_box, int64_t nf, int32_t natoms,
                        const int32_t* h_res_start, int32_t nres, int32_t symmetric, int32_t x0,
                        int32_t xres, int32_t y0, int32_t yres, float trunc, int32_t nlevels,
                        int32_t pbc, uint16_t* d_levels, int64_t levels_stride,
-                       unsigned long long* d_n_boundary, void* d_work, size_t work_bytes,
+                       unsigned long long* d_counters, void* d_work, size_t work_bytes,
                        void* stream);
+
+/* Same call split for measurement: phases bit 0 = the coordinate re-layout / bounding-sphere pass,
+ * bit 1 = the tile kernel (which needs the workspace left by a bit-0 call on the same frames).
+ * conan_mdmat_frames is phases = 3.  bench.py times the two kernels separately with this. */
+int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int64_t nf, int32_t natoms,
+                          const int32_t* h_res_start, int32_t nres, int32_t symmetric, int32_t x0,
+                          int32_t xres, int32_t y0, int32_t yres, float trunc, int32_t nlevels,
+                          int32_t pbc, uint16_t* d_levels, int64_t levels_stride,
+                          unsigned long long* d_counters, void* d_work, size_t work_bytes,
+                          void* stream, int32_t phases);
 
 /* ------------------------------------------------------------------------------------ */
 /* Stage 2: streaming per-pair statistics over a level stack.  Replaces the per-frame     */
@@ -152,6 +164,16 @@ size_t conan_pair_stats_workspace_bytes(int64_t nf, int64_t P);
  *           NULL = all off.
  * Work is split into frame chunks x pair tiles inside; chunk records live in d_work.
  */
+/* With recombine != 0 the streaming pass is skipped and the chunk records left in d_work by the
+ * previous call with the same (nf, P) are folded again under a new d_status_in: how a frame shard
+ * learns its entering status after the shards' summaries have been exchanged. */
+int conan_pair_stats_ex(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                        int64_t frame0, int32_t nlevels, int32_t lo_cnt, int32_t hi_first,
+                        int32_t equal_cut, const uint16_t* d_first_row, const uint16_t* d_prev_row,
+                        const uint8_t* d_status_in, const conan_pair_stats_out* out,
+                        const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
+                        void* stream, int32_t recombine);
+
 int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
                      int64_t frame0, int32_t nlevels, int32_t lo_cnt, int32_t hi_first,
                      int32_t equal_cut,

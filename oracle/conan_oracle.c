@@ -393,20 +393,52 @@ int orc_mdmat_levels(const float *xyz, const float *box, int nf, int natoms,
  *   native, nonnative [nf] int32; ssd_prev, ssd_first [nf] int64 (sum over pairs of squared
  *   level differences to the previous / first frame; frame 0 gets 0).
  */
+int orc_pair_stats_shard(const uint16_t *levels, int nf, int64_t P, int lo_cnt, int hi_first,
+                         int equal_cut, int frame0, const uint16_t *first_row,
+                         const uint16_t *prev_row, const uint8_t *status_in, int64_t *sum_k,
+                         int64_t *sum_k2, int32_t *n_int, int32_t *n_enc, int32_t *first_f,
+                         int32_t *last_f, uint8_t *status, uint16_t *kmin, uint16_t *kmax,
+                         int32_t *native, int32_t *nonnative, int64_t *ssd_prev,
+                         int64_t *ssd_first, uint8_t *decided);
+
 int orc_pair_stats(const uint16_t *levels, int nf, int64_t P, int lo_cnt, int hi_first,
                    int equal_cut, int64_t *sum_k, int64_t *sum_k2, int32_t *n_int,
                    int32_t *n_enc, int32_t *first_f, int32_t *last_f, uint8_t *status,
                    uint16_t *kmin, uint16_t *kmax, int32_t *native, int32_t *nonnative,
                    int64_t *ssd_prev, int64_t *ssd_first) {
+    return orc_pair_stats_shard(levels, nf, P, lo_cnt, hi_first, equal_cut, 0, NULL, NULL, NULL,
+                                sum_k, sum_k2, n_int, n_enc, first_f, last_f, status, kmin, kmax,
+                                native, nonnative, ssd_prev, ssd_first, NULL);
+}
+
+/*
+ * The same loop for a shard of a longer trajectory: frame numbers start at frame0, the
+ * interaction status entering the shard is status_in (NULL = off), "native" and the
+ * rmsd-to-first reference come from first_row (NULL = this shard's first row), and prev_row
+ * (NULL = none) is the frame before the shard.  decided[p] (optional) is set when some frame
+ * of the shard was outside the hysteresis buffer.
+ */
+int orc_pair_stats_shard(const uint16_t *levels, int nf, int64_t P, int lo_cnt, int hi_first,
+                         int equal_cut, int frame0, const uint16_t *first_row,
+                         const uint16_t *prev_row, const uint8_t *status_in, int64_t *sum_k,
+                         int64_t *sum_k2, int32_t *n_int, int32_t *n_enc, int32_t *first_f,
+                         int32_t *last_f, uint8_t *status, uint16_t *kmin, uint16_t *kmax,
+                         int32_t *native, int32_t *nonnative, int64_t *ssd_prev,
+                         int64_t *ssd_first, uint8_t *decided) {
     uint8_t *nat = (uint8_t *)calloc((size_t)P, 1);
     if (!nat) return -2;
+    if (!first_row) first_row = levels;
+    if (equal_cut) hi_first = lo_cnt;
     for (int64_t p = 0; p < P; p++) {
         sum_k[p] = 0; sum_k2[p] = 0; n_int[p] = 0; n_enc[p] = 0;
-        first_f[p] = -1; last_f[p] = -1; status[p] = 0; kmin[p] = 65535; kmax[p] = 0;
+        first_f[p] = -1; last_f[p] = -1; status[p] = status_in ? status_in[p] : 0;
+        kmin[p] = 65535; kmax[p] = 0;
+        nat[p] = (uint8_t)(first_row[p] < lo_cnt);
+        if (decided) decided[p] = 0;
     }
     for (int f = 0; f < nf; f++) {
         const uint16_t *row = levels + (size_t)P * f;
-        const uint16_t *prev = f ? row - P : row;
+        const uint16_t *prev = f ? row - P : (prev_row ? prev_row : row);
         int32_t nn = 0, nno = 0;
         int64_t sp = 0, s0 = 0;
         for (int64_t p = 0; p < P; p++) {
@@ -420,18 +452,18 @@ int orc_pair_stats(const uint16_t *levels, int nf, int64_t P, int lo_cnt, int hi
             else if (k < lo_cnt) ns = 1;
             else if (k >= hi_first) ns = 0;
             else ns = st;
+            if (decided && (k < lo_cnt || k >= hi_first)) decided[p] = 1;
             if (ns) {
                 n_int[p]++;
-                last_f[p] = f;
+                last_f[p] = frame0 + f;
                 if (!st) {
-                    if (first_f[p] < 0) first_f[p] = f;
+                    if (first_f[p] < 0) first_f[p] = frame0 + f;
                     n_enc[p]++;
                 }
             }
             status[p] = (uint8_t)ns;
-            if (f == 0) nat[p] = (uint8_t)ns;
             if (ns) { if (nat[p]) nn++; else nno++; }
-            int64_t dp = (int64_t)k - prev[p], d0 = (int64_t)k - levels[p];
+            int64_t dp = (int64_t)k - prev[p], d0 = (int64_t)k - first_row[p];
             sp += dp * dp;
             s0 += d0 * d0;
         }

@@ -33,6 +33,8 @@ def load():
         _lib.orc_mdmat_levels.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_int, ctypes.c_int,
                                           ctypes.c_float, ctypes.c_int, ctypes.c_int, vp]
         _lib.orc_pair_stats.argtypes = [vp, ctypes.c_int, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int] + [vp] * 13
+        _lib.orc_pair_stats_shard.argtypes = [vp, ctypes.c_int, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_int, vp, vp, vp] + [vp] * 14
     return _lib
 
 
@@ -96,19 +98,25 @@ def legend_values(trunc, nlevels):
     return np.array(vals, dtype=np.float64)
 
 
-def pair_stats(levels, lo_cnt, hi_first, equal_cut):
-    """C restatement of the frame loop (conan.py:782-874) over a [nf, P] level stack."""
+def pair_stats(levels, lo_cnt, hi_first, equal_cut, frame0=0, first_row=None, prev_row=None, status_in=None):
+    """C restatement of the frame loop (conan.py:782-874) over a [nf, P] level stack.
+
+    The keyword arguments describe a shard of a longer trajectory (see orc_pair_stats_shard)."""
     lib = load()
     levels = np.ascontiguousarray(levels, np.uint16)
     nf, P = levels.shape
+    keep = [None if a is None else np.ascontiguousarray(a, dt) for a, dt in
+            ((first_row, np.uint16), (prev_row, np.uint16), (status_in, np.uint8))]
+    ptr = [None if a is None else a.ctypes.data for a in keep]
     o = dict(sum_k=np.zeros(P, np.int64), sum_k2=np.zeros(P, np.int64), n_int=np.zeros(P, np.int32),
              n_enc=np.zeros(P, np.int32), first_f=np.zeros(P, np.int32), last_f=np.zeros(P, np.int32),
              status=np.zeros(P, np.uint8), kmin=np.zeros(P, np.uint16), kmax=np.zeros(P, np.uint16),
              native=np.zeros(nf, np.int32), nonnative=np.zeros(nf, np.int32),
-             ssd_prev=np.zeros(nf, np.int64), ssd_first=np.zeros(nf, np.int64))
+             ssd_prev=np.zeros(nf, np.int64), ssd_first=np.zeros(nf, np.int64), decided=np.zeros(P, np.uint8))
     order = ["sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f", "status", "kmin", "kmax",
-             "native", "nonnative", "ssd_prev", "ssd_first"]
-    rc = lib.orc_pair_stats(levels.ctypes.data, nf, P, lo_cnt, hi_first, equal_cut, *[o[k].ctypes.data for k in order])
+             "native", "nonnative", "ssd_prev", "ssd_first", "decided"]
+    rc = lib.orc_pair_stats_shard(levels.ctypes.data, nf, P, lo_cnt, hi_first, equal_cut, frame0, *ptr,
+                                  *[o[k].ctypes.data for k in order])
     if rc != 0:
         raise ValueError("orc_pair_stats failed: %d" % rc)
     return o
