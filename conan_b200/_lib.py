@@ -54,6 +54,9 @@ SIGNATURES = {
     "conan_mdmat_frames_ex": (ctypes.c_int, [c_void_p, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_i32,
                                              c_i32, c_i32, c_i32, c_i32, c_f32, c_i32, c_i32, c_void_p,
                                              c_i64, c_void_p, c_void_p, c_size, c_void_p, c_i32]),
+    "conan_mdmat_frames_static": (ctypes.c_int, [c_void_p, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_i32,
+                                                 c_i32, c_i32, c_i32, c_i32, c_f32, c_i32, c_i32, c_void_p,
+                                                 c_i64, c_void_p, c_void_p]),
     "conan_pair_stats_ex": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32,
                                            c_i32, c_void_p, c_void_p, c_void_p,
                                            ctypes.POINTER(PairStatsOut), ctypes.POINTER(FrameStatsOut),

@@ -26,6 +26,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 
 #include "common.h"
 
@@ -583,4 +584,64 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
         CONAN_CUDA_TRY(cudaGetLastError());
     }
     return CONAN_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free variant of stage 1
+// ------------------------------------------------------------------------------------------
+// Some callers of this library are not in a position to hand over a workspace: an analysis hook
+// that runs inside another program's time-step loop (contact maps computed on the fly while an
+// MD engine is integrating) must not call cudaMalloc / cudaFree, because those synchronise the
+// whole device and stall the engine's streams, and late in a run the engine's own pools may have
+// left no memory to allocate from.  For them the scratch that conan_mdmat_frames normally takes
+// from the caller lives in this fixed array, which every GPU that loads the library carries
+// until the process exits.
+static __device__ __align__(256) unsigned char g_mdmat_static_scratch[CONAN_MDMAT_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_static_scratch_ptr[kMaxDevices] = {nullptr};
+std::mutex g_static_scratch_mutex;
+}  // namespace
+
+extern "C" int conan_mdmat_frames_static(const float* d_xyz, const float* d_box, int64_t nf, int32_t natoms,
+                                         const int32_t* h_res_start, int32_t nres, int32_t symmetric,
+                                         int32_t x0, int32_t xres, int32_t y0, int32_t yres, float trunc,
+                                         int32_t nlevels, int32_t pbc, uint16_t* d_levels,
+                                         int64_t levels_stride, unsigned long long* d_counters,
+                                         void* stream_) {
+    int dev = -1;
+    CONAN_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices)
+        return conan::fail(CONAN_ERR_SIZE, "conan_mdmat_frames_static: device ordinal %d not supported (max %d)", dev, kMaxDevices - 1);
+    void* scratch = nullptr;
+    {
+        // Set-up, once per device and with that device current: in host code the array's name is
+        // only a stand-in for the symbol, so its device address has to be asked for.
+        std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+        if (!g_static_scratch_ptr[dev]) {
+            void* p = nullptr;
+            CONAN_CUDA_TRY(cudaGetSymbolAddress(&p, g_mdmat_static_scratch));
+            g_static_scratch_ptr[dev] = p;
+        }
+        scratch = g_static_scratch_ptr[dev];
+    }
+    if (!h_res_start || nres <= 0 || natoms <= 0 || nf < 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_mdmat_frames_static: bad argument");
+    int max_atoms = 0;
+    for (int r = 0; r < nres; r++) {
+        const int n = h_res_start[r + 1] - h_res_start[r];
+        if (n > max_atoms) max_atoms = n;
+    }
+    const size_t need = nf > 0 ? conan_mdmat_workspace_bytes(nf, natoms, nres, max_atoms > 0 ? max_atoms : 1) : 0;
+    if (need > (size_t)CONAN_MDMAT_STATIC_SCRATCH_BYTES)
+        return conan::fail(CONAN_ERR_SIZE,
+                           "conan_mdmat_frames_static: %lld frames of %d residues need %zu bytes of scratch but the "
+                           "built-in scratch holds %zu; pass fewer frames per call or use conan_mdmat_frames",
+                           (long long)nf, nres, need, (size_t)CONAN_MDMAT_STATIC_SCRATCH_BYTES);
+    // Nothing in the scratch has to start at zero: the first kernel of the call rewrites every
+    // byte that the second one reads, so whatever an earlier call left behind is never seen.
+    return conan_mdmat_frames_ex(d_xyz, d_box, nf, natoms, h_res_start, nres, symmetric, x0, xres, y0, yres, trunc,
+                                 nlevels, pbc, d_levels, levels_stride, d_counters, scratch,
+                                 (size_t)CONAN_MDMAT_STATIC_SCRATCH_BYTES, stream_, 3);
 }

@@ -62,6 +62,26 @@ def mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, pbc, d_levels, d_work, d_co
     return d_levels
 
 
+STATIC_SCRATCH_BYTES = 32 * 1024 * 1024   # CONAN_MDMAT_STATIC_SCRATCH_BYTES
+
+
+def mdmat_frames_static(d_xyz, d_box, geom, trunc, nlevels, pbc, d_levels, d_counters=None, stream=None):
+    """Stage 1 through conan_mdmat_frames_static: no workspace tensor, nothing allocated.
+
+    For hosts that must not allocate device memory while they run (an analysis hook inside a
+    simulation's step loop); limited to the frames whose scratch fits STATIC_SCRATCH_BYTES."""
+    lib = _lib.load()
+    if not d_xyz.is_cuda:
+        raise _lib.ConanError(-1, "stage 1 needs device tensors: there is no CPU fallback")
+    nf = d_xyz.shape[0]
+    s = stream if stream is not None else torch.cuda.current_stream(d_xyz.device)
+    _lib.check(lib.conan_mdmat_frames_static(
+        d_xyz.data_ptr(), _ptr(d_box), nf, geom.natoms, geom.res_start.ctypes.data, geom.nres,
+        1 if geom.symmetric else 0, geom.x0, geom.xres, geom.y0, geom.yres, float(trunc), int(nlevels),
+        1 if pbc else 0, d_levels.data_ptr(), geom.stride, _ptr(d_counters), s.cuda_stream))
+    return d_levels
+
+
 def compute_levels(xyz, boxes, geom, trunc, nlevels, pbc=False, device="cuda", batch=4096, out=None):
     """Host coordinates [nf, natoms, 3] -> device level stack [nf, stride] uint16, batched H2D."""
     xyz = np.ascontiguousarray(xyz, dtype=np.float32)

@@ -117,6 +117,31 @@ int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int64_t nf, in
                           unsigned long long* d_counters, void* d_work, size_t work_bytes,
                           void* stream, int32_t phases);
 
+/*
+ * conan_mdmat_frames without a workspace argument.  This entry point has no counterpart in the
+ * reference; it exists for callers that cannot allocate device memory at all -- for example an
+ * on-the-fly analysis hook called from inside a running simulation's step loop, where
+ * cudaMalloc / cudaFree would synchronise the device and stall the host program's streams, or
+ * where that program's memory pools have already claimed the GPU.  The scratch is a fixed
+ * CONAN_MDMAT_STATIC_SCRATCH_BYTES array inside the library (resident on every GPU that loads
+ * the library, until the process exits), so a call is limited to as many frames as
+ *     conan_mdmat_workspace_bytes(nf, natoms, nres, max_res_atoms) <= CONAN_MDMAT_STATIC_SCRATCH_BYTES
+ * allows (about 290 frames of a 1000-residue, 8-atoms-per-residue system); larger calls return
+ * CONAN_ERR_SIZE and must be split.  It calls no cudaMalloc, cudaFree or other allocating routine.
+ * The first call on each device looks up the array's device address; make that first call
+ * before starting any stream capture.  All calls on a device share the one array, which keeps the
+ * previous call's contents (nothing in it needs to start at zero: each call rewrites what it
+ * reads); two calls whose GPU work overlaps -- different streams, or different host threads --
+ * race on it, so issue them on one stream or otherwise order them.
+ * Arguments and results are otherwise exactly those of conan_mdmat_frames.
+ */
+#define CONAN_MDMAT_STATIC_SCRATCH_BYTES (32u * 1024u * 1024u)
+int conan_mdmat_frames_static(const float* d_xyz, const float* d_box, int64_t nf, int32_t natoms,
+                              const int32_t* h_res_start, int32_t nres, int32_t symmetric, int32_t x0,
+                              int32_t xres, int32_t y0, int32_t yres, float trunc, int32_t nlevels,
+                              int32_t pbc, uint16_t* d_levels, int64_t levels_stride,
+                              unsigned long long* d_counters, void* stream);
+
 /* ------------------------------------------------------------------------------------ */
 /* Stage 2: streaming per-pair statistics over a level stack.  Replaces the per-frame     */
 /* loop of read_process_frames, conan.py:782-874, with update_aggregate :599-611,         */
