@@ -235,7 +235,7 @@ def run_ours(args):
         launches[0] += 2
         if world > 1:
             sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
-            launches[0] += 5
+            launches[0] += 4
         else:
             stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2)
             launches[0] += 3

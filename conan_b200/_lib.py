@@ -29,8 +29,7 @@ class ConanError(RuntimeError):
 
 class PairStatsOut(ctypes.Structure):
     _fields_ = [(n, c_void_p) for n in (
-        "d_sum_k", "d_sum_k2", "d_n_int", "d_n_enc", "d_first_f", "d_last_f", "d_status",
-        "d_kmin", "d_kmax", "d_decided")]
+        "d_sum_k", "d_sum_k2", "d_n_int", "d_n_enc", "d_first_f", "d_last_f", "d_status", "d_decided")]
 
 
 class FrameStatsOut(ctypes.Structure):
@@ -57,10 +56,8 @@ SIGNATURES = {
     "conan_mdmat_frames_static": (ctypes.c_int, [c_void_p, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_i32,
                                                  c_i32, c_i32, c_i32, c_i32, c_f32, c_i32, c_i32, c_void_p,
                                                  c_i64, c_void_p, c_void_p]),
-    "conan_pair_stats_ex": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32,
-                                           c_i32, c_void_p, c_void_p, c_void_p,
-                                           ctypes.POINTER(PairStatsOut), ctypes.POINTER(FrameStatsOut),
-                                           c_void_p, c_size, c_void_p, c_i32]),
+    "conan_shard_summary": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32, c_i32,
+                                           c_void_p, c_void_p, c_void_p]),
     "conan_pair_stats_workspace_bytes": (c_size, [c_i64, c_i64]),
     "conan_pair_stats": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32,
                                         c_i32, c_void_p, c_void_p, c_void_p,

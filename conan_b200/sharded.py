@@ -4,10 +4,10 @@ Frames are independent for stage 1, so every rank computes the level stack of it
 frame range.  Stage 2 needs three small exchanges:
   1. the level row of GLOBAL frame 0 (defines "native" contacts and the rmsd-to-first reference)
      and the last row of the preceding shard (rmsd-to-previous of the shard's first frame);
-  2. the interaction status entering each shard: every rank first runs under "enter off" and
-     publishes, per pair, whether its shard saw a decisive frame and the status it leaves with;
-     an exclusive scan over ranks gives the true entering status, and the chunk records are
-     folded once more under it (conan_pair_stats_ex recombine, no second pass over the stack);
+  2. the interaction status entering each shard: every rank publishes, per pair, whether its shard
+     has a frame outside the hysteresis buffer and the status it then leaves with
+     (conan_shard_summary, a short backward scan from the shard's end); an exclusive scan over
+     ranks gives the status entering every shard before the streaming pass runs;
   3. the per-pair sums: all-reduce SUM of the integer moments and counts, MIN / MAX of the
      first / last frame and level extremes.  Integer sums make the merge exact and
      order-independent.
@@ -22,14 +22,6 @@ _INT_MAX = 2 ** 31 - 1
 def _raw(t):
     """Byte view for pure data movement (the collectives have no 16-bit unsigned type)."""
     return t.contiguous().view(torch.uint8)
-
-
-def _reduce16(t, op, group):
-    """MIN / MAX of a 16-bit level tensor through int32 (levels are < 7744)."""
-    signed = t.view(torch.int16) if t.dtype == torch.uint16 else t
-    wide = signed.to(torch.int32)
-    dist.all_reduce(wide, op=op, group=group)
-    signed.copy_(wide.to(torch.int16))
 
 
 def exchange_rows(first_row_local, last_row_local, group=None):
@@ -68,8 +60,6 @@ def merge_pair_stats(st, group=None):
     dist.all_reduce(first, op=dist.ReduceOp.MIN, group=group)
     first.copy_(torch.where(first == _INT_MAX, torch.full_like(first, -1), first))
     dist.all_reduce(st.last_f, op=dist.ReduceOp.MAX, group=group)
-    _reduce16(st.kmin, dist.ReduceOp.MIN, group)
-    _reduce16(st.kmax, dist.ReduceOp.MAX, group)
     dist.all_reduce(st.decided, op=dist.ReduceOp.MAX, group=group)
     # the status after the last frame is the last shard's
     src = dist.get_global_rank(group, world - 1) if group is not None else world - 1
@@ -78,19 +68,17 @@ def merge_pair_stats(st, group=None):
 
 
 def pair_stats_sharded(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0, out=None, work=None, group=None,
-                       local_pass=None):
+                       local_pass=None, local_summary=None):
     """Stage 2 over this rank's frame shard, merged so that per-pair results equal a single run.
 
-    Per-frame results stay local to the rank (frames are disjoint).  `local_pass` exists for the
-    CPU tests: a callable with the signature of stage2.pair_stats."""
+    Per-frame results stay local to the rank (frames are disjoint).  `local_pass` / `local_summary`
+    exist for the CPU tests: callables with the signatures of stage2.pair_stats / shard_summary."""
     if local_pass is None:
         from . import stage2
-        local_pass = stage2.pair_stats
+        local_pass, local_summary = stage2.pair_stats, stage2.shard_summary
     first_row, prev_row = exchange_rows(levels[0], levels[-1], group)
+    decided, status = local_summary(levels, P, nlevels, lo_cnt, hi_first, equal_cut)
+    s_in = entering_status(decided, status, group)
     st = local_pass(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=frame0, first_row=first_row,
-                    prev_row=prev_row, status_in=None, out=out, work=work)
-    s_in = entering_status(st.decided, st.status, group)
-    if dist.get_rank(group) > 0:
-        st = local_pass(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=frame0, first_row=first_row,
-                        prev_row=prev_row, status_in=s_in, out=st, work=getattr(st, "work", work), recombine=True)
+                    prev_row=prev_row, status_in=s_in, out=out, work=work)
     return merge_pair_stats(st, group)

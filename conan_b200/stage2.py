@@ -15,8 +15,7 @@ class PairStats:
 
     PAIR_FIELDS = (("sum_k", torch.int64), ("sum_k2", torch.int64), ("n_int", torch.int32),
                    ("n_enc", torch.int32), ("first_f", torch.int32), ("last_f", torch.int32),
-                   ("status", torch.uint8), ("kmin", torch.uint16), ("kmax", torch.uint16),
-                   ("decided", torch.uint8))
+                   ("status", torch.uint8), ("decided", torch.uint8))
     FRAME_FIELDS = (("native", torch.int32), ("nonnative", torch.int32), ("ssd_prev", torch.int64),
                     ("ssd_first", torch.int64))
 
@@ -47,7 +46,7 @@ def pair_stats_workspace_bytes(nf, P):
 
 
 def pair_stats(d_levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=0, first_row=None, prev_row=None,
-               status_in=None, out=None, work=None, stream=None, recombine=False):
+               status_in=None, out=None, work=None, stream=None):
     """Launch stage 2 on a device level stack [nf, stride] (uint16); returns PairStats (device)."""
     lib = _lib.load()
     if not d_levels.is_cuda:
@@ -62,9 +61,24 @@ def pair_stats(d_levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=0, firs
     fo = _lib.FrameStatsOut(*[getattr(out, n).data_ptr() for n, _ in PairStats.FRAME_FIELDS])
     s = stream if stream is not None else torch.cuda.current_stream(dev)
     ptr = lambda t: 0 if t is None else t.data_ptr()
-    _lib.check(lib.conan_pair_stats_ex(d_levels.data_ptr(), stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
-                                       ptr(first_row), ptr(prev_row), ptr(status_in), ctypes.byref(po), ctypes.byref(fo),
-                                       work.data_ptr(), work.numel(), s.cuda_stream, 1 if recombine else 0))
+    _lib.check(lib.conan_pair_stats(d_levels.data_ptr(), stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
+                                    ptr(first_row), ptr(prev_row), ptr(status_in), ctypes.byref(po), ctypes.byref(fo),
+                                    work.data_ptr(), work.numel(), s.cuda_stream))
     out.work = work
     out._keepalive = (first_row, prev_row, status_in)
     return out
+
+
+def shard_summary(d_levels, P, nlevels, lo_cnt, hi_first, equal_cut, stream=None):
+    """(decided, status) uint8 device tensors of a frame shard (conan_shard_summary)."""
+    lib = _lib.load()
+    if not d_levels.is_cuda:
+        raise _lib.ConanError(-1, "stage 2 needs device tensors: there is no CPU fallback")
+    nf, stride = d_levels.shape
+    dev = d_levels.device
+    decided = torch.empty(P, dtype=torch.uint8, device=dev)
+    status = torch.empty(P, dtype=torch.uint8, device=dev)
+    s = stream if stream is not None else torch.cuda.current_stream(dev)
+    _lib.check(lib.conan_shard_summary(d_levels.data_ptr(), stride, nf, P, nlevels, lo_cnt, hi_first, equal_cut,
+                                       decided.data_ptr(), status.data_ptr(), s.cuda_stream))
+    return decided, status

@@ -70,8 +70,8 @@ class Stage2Tables:
         # :913-916 with the cancellation done in exact integer arithmetic
         var_num = tn * sum_k2 - sum_k * sum_k
         self.std = dx * np.sqrt(np.maximum(var_num, 0).astype(np.float64)) / tn
-        self.seen = stats["kmin"] < nl - 1                            # pair ever below trunc (:536-537)
-        self.varying = stats["kmin"] != stats["kmax"]
+        self.seen = sum_k < tn * (nl - 1)                             # pair ever below trunc (:536-537)
+        self.varying = var_num != 0                                   # len(set(rvec)) > 1 (:1902)
         # per-frame lines
         self.native = stats["native"].astype(np.int64)
         self.nonnative = stats["nonnative"].astype(np.int64)

@@ -149,7 +149,10 @@ int conan_mdmat_frames_static(const float* d_xyz, const float* d_box, int64_t nf
 /* :1414-1432 (called from plot_frames :643-644).                                         */
 /* ------------------------------------------------------------------------------------ */
 
-/* Per-pair results; every array has P entries and is written, not accumulated. */
+/* Per-pair results; every array has P entries and is written, not accumulated.  Two facts the
+ * reference tracks separately follow from the exact sums: a pair is in pairs_list (ever below
+ * trunc, :528-539) iff sum_k < nf*(nlevels-1), and its series is constant (the len(set(rvec)) > 1
+ * test, :1902) iff nf*sum_k2 == sum_k^2. */
 typedef struct conan_pair_stats_out {
     int64_t* d_sum_k;    /* sum over frames of the level index            (-> sum r,  :601) */
     int64_t* d_sum_k2;   /* sum of squared level indices                  (-> sum r^2, :602) */
@@ -158,9 +161,7 @@ typedef struct conan_pair_stats_out {
     int32_t* d_first_f;  /* first frame with the interaction on, -1 never (:608-609) */
     int32_t* d_last_f;   /* last frame with the interaction on, -1 never  (:606) */
     uint8_t* d_status;   /* status after the last frame                   (:611) */
-    uint16_t* d_kmin;    /* smallest level seen (pair is in pairs_list iff kmin < nlevels-1, :528-539) */
-    uint16_t* d_kmax;    /* largest level seen (kmin != kmax is the len(set(rvec)) > 1 test, :1902) */
-    uint8_t* d_decided;  /* 1 if some frame of this call was outside the hysteresis buffer */
+    uint8_t* d_decided;  /* optional: 1 if some frame of this call was outside the hysteresis buffer */
 } conan_pair_stats_out;
 
 /* Per-frame results; nf entries each, frame numbering local to the call. */
@@ -187,18 +188,9 @@ size_t conan_pair_stats_workspace_bytes(int64_t nf, int64_t P);
  *           first frame then gets ssd_prev 0, as the reference's first frame writes no line).
  * d_status_in [P] interaction status entering this call (frame shards after the first);
  *           NULL = all off.
- * Work is split into frame chunks x pair tiles inside; chunk records live in d_work.
+ * Work is split into frame chunks x pair tiles inside; the status entering each chunk is found
+ * by a short backward scan from the chunk boundary, chunk records live in d_work.
  */
-/* With recombine != 0 the streaming pass is skipped and the chunk records left in d_work by the
- * previous call with the same (nf, P) are folded again under a new d_status_in: how a frame shard
- * learns its entering status after the shards' summaries have been exchanged. */
-int conan_pair_stats_ex(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
-                        int64_t frame0, int32_t nlevels, int32_t lo_cnt, int32_t hi_first,
-                        int32_t equal_cut, const uint16_t* d_first_row, const uint16_t* d_prev_row,
-                        const uint8_t* d_status_in, const conan_pair_stats_out* out,
-                        const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
-                        void* stream, int32_t recombine);
-
 int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
                      int64_t frame0, int32_t nlevels, int32_t lo_cnt, int32_t hi_first,
                      int32_t equal_cut,
@@ -206,6 +198,15 @@ int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride, int64_t nf
                      const uint8_t* d_status_in, const conan_pair_stats_out* out,
                      const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
                      void* stream);
+
+/* Summary of a frame shard for the exchange between GPUs (no counterpart in the reference, which
+ * is single-process): d_decided[p] = 1 if some frame of the shard lies outside the hysteresis
+ * buffer, and then d_status[p] is the interaction status after the shard's last frame whatever
+ * the status entering it.  An exclusive scan of these summaries over the shards gives every
+ * shard's d_status_in for conan_pair_stats.  Reads only the few trailing rows it needs. */
+int conan_shard_summary(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                        int32_t nlevels, int32_t lo_cnt, int32_t hi_first, int32_t equal_cut,
+                        uint8_t* d_decided, uint8_t* d_status, void* stream);
 
 /* ------------------------------------------------------------------------------------ */
 /* Measurement helpers (bench.py only).                                                  */

@@ -4,7 +4,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-PAIR_KEYS = ("sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f", "status", "kmin", "kmax")
+PAIR_KEYS = ("sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f", "status")
 FRAME_KEYS = ("native", "nonnative", "ssd_prev", "ssd_first")
 
 
@@ -84,7 +84,10 @@ def test_frame_shards_compose(lib, orc):
     assert np.array_equal(np.where(ha["first_f"] >= 0, ha["first_f"], hb["first_f"]), want["first_f"])
     assert np.array_equal(np.maximum(ha["last_f"], hb["last_f"]), want["last_f"])
     assert np.array_equal(hb["status"], want["status"])
-    assert np.array_equal(np.minimum(ha["kmin"], hb["kmin"]), want["kmin"])
+    # the shard summary used between GPUs: decided + leaving status of the first shard
+    dec, sta = stage2.shard_summary(d[:cut], P, 1001, 500, 601, 0)
+    assert np.array_equal(dec.cpu().numpy(), ha["decided"])
+    assert np.array_equal(np.where(ha["decided"] != 0, sta.cpu().numpy(), 0), np.where(ha["decided"] != 0, ha["status"], 0))
     for k in FRAME_KEYS:
         assert np.array_equal(np.concatenate([ha[k], hb[k]]), want[k]), k
 

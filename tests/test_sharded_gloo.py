@@ -21,7 +21,7 @@ class _Stats:
 
 
 def _oracle_pass(levels, P, nlevels, lo, hi, eq, frame0=0, first_row=None, prev_row=None, status_in=None, out=None,
-                 work=None, recombine=False):
+                 work=None):
     from oracle import oracle
     n = lambda t: None if t is None else t.numpy().view(np.uint16) if t.dtype == torch.int16 else t.numpy()
     o = oracle.pair_stats(n(levels)[:, :P], lo, hi, eq, frame0=frame0,
@@ -32,6 +32,17 @@ def _oracle_pass(levels, P, nlevels, lo, hi, eq, frame0=0, first_row=None, prev_
     for k, v in o.items():
         setattr(st, k, torch.from_numpy(v.view(np.int16) if v.dtype == np.uint16 else v))
     return st
+
+
+def _oracle_summary(levels, P, nlevels, lo, hi, eq):
+    lv = (levels.numpy().view(np.uint16) if levels.dtype == torch.int16 else levels.numpy())[:, :P].astype(np.int64)
+    if eq:
+        hi = lo
+    decisive = (lv < lo) | (lv >= hi)
+    decided = decisive.any(axis=0)
+    last = lv.shape[0] - 1 - np.argmax(decisive[::-1], axis=0)
+    status = (lv[last, np.arange(P)] < lo) & decided
+    return torch.from_numpy(decided.astype(np.uint8)), torch.from_numpy(status.astype(np.uint8))
 
 
 def _worker(rank, world, port, nf, P, seed, tmp):
@@ -48,10 +59,10 @@ def _worker(rank, world, port, nf, P, seed, tmp):
     levels = np.rint(r * 100).astype(np.uint16)
     bounds = np.linspace(0, nf, world + 1).astype(int)
     mine = torch.from_numpy(levels[bounds[rank]:bounds[rank + 1]].view(np.int16).copy())
-    st = sharded.pair_stats_sharded(mine, P, 101, 50, 61, 0, frame0=int(bounds[rank]), local_pass=_oracle_pass)
+    st = sharded.pair_stats_sharded(mine, P, 101, 50, 61, 0, frame0=int(bounds[rank]), local_pass=_oracle_pass,
+                                    local_summary=_oracle_summary)
     res = {k: getattr(st, k).numpy().copy() for k in ("sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f",
-                                                     "status", "kmin", "kmax", "native", "nonnative", "ssd_prev",
-                                                     "ssd_first")}
+                                                     "status", "native", "nonnative", "ssd_prev", "ssd_first")}
     np.savez(os.path.join(tmp, "rank%d.npz" % rank), levels=levels, **res)
     dist.destroy_process_group()
 
@@ -75,7 +86,5 @@ def test_sharded_stats_equal_single_run(orc, tmp_path, world, nf):
     for r in ranks:      # per-pair results are identical on every rank and equal the single run
         for k in ("sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f", "status"):
             assert np.array_equal(r[k], want[k]), k
-        assert np.array_equal(r["kmin"].view(np.uint16), want["kmin"])
-        assert np.array_equal(r["kmax"].view(np.uint16), want["kmax"])
     for k in ("native", "nonnative", "ssd_prev", "ssd_first"):   # per-frame results concatenate
         assert np.array_equal(np.concatenate([r[k] for r in ranks]), want[k]), k
