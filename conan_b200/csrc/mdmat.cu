@@ -7,19 +7,25 @@
 //
 // Two kernels:
 //   prep_slots_kernel   [nf][natoms][3] coordinates -> a TMA-friendly "slot" layout
-//                       slots[f][c][k][res] (c = x/y/z, k = atom slot inside the residue, residues
-//                       padded to a multiple of the tile; empty slots repeat the residue's first
-//                       atom so a minimum over slots is unaffected) plus one bounding sphere per
-//                       residue.
-//   mdmat_tile_kernel   one CTA per (frame, 64x64 residue tile).  Thread 0 issues the TMA tile
-//                       loads (cp.async.bulk.tensor.4d) for the two residue tiles; while they are
-//                       in flight all threads prune residue pairs by bounding sphere and compact
-//                       the survivors into a shared-memory list; survivors then get the exact
-//                       float32 minimum over atom pairs (same operation order as the CPU
-//                       restatement: no FMA contraction), sqrt, level = rint(r*invlevel); the
-//                       64x64 uint16 tile is staged in shared memory and written out row-wise.
+//                       slots[f][plane][k][res]: every residue's atoms relative to the residue's own
+//                       centre, once as (x', y', z') and once pre-scaled for the expanded distance
+//                       form as (-2x', -2y', -2z', |a'|^2); k = atom slot inside the residue,
+//                       residues padded to a multiple of the tile, empty slots repeat the residue's
+//                       first atom (a minimum over slots is unaffected); plus one bounding sphere
+//                       (centre, radius) per residue.
+//   mdmat_tile_kernel   one CTA per (64x64 residue tile, group of up to 4 consecutive frames).
+//                       Thread 0 issues two TMA tile loads (cp.async.bulk.tensor.4d) covering the
+//                       whole frame group; meanwhile the CTA fills its part of the output with the
+//                       "beyond trunc" level and prunes residue pairs by bounding sphere, compacting
+//                       the survivors of all frames into one shared-memory list.  Survivors are
+//                       evaluated in the expanded form |b'+D|^2 - 2a'.(b'+D) + |a'|^2 (3 FMA + 1 min
+//                       per atom pair) with a rigorous rounding bound E; if every value in
+//                       [m-E, m+E] quantises to the same level that level is final, otherwise the
+//                       pair is redone with the reference operation order (no FMA contraction) from
+//                       the original coordinates, which is also the path for pairs that may need a
+//                       periodic shift.  Results are therefore bit-identical to the CPU restatement.
 //
-// The kernel is FP32-pipe bound (8 flops per atom pair that survives pruning); see DESIGN.md.
+// The kernel is bound by FP32 / integer instruction issue; see DESIGN.md.
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -32,10 +38,18 @@
 
 namespace {
 
-constexpr int kTile = 64;        // residues per tile side
-constexpr int kThreads = 256;    // threads per CTA of mdmat_tile_kernel
-constexpr int kMaxKpad = 128;    // largest supported atoms-per-residue (after padding to 4)
+constexpr int kTile = 64;          // residues per tile side
+constexpr int kThreads = 256;      // threads per CTA of mdmat_tile_kernel
+constexpr int kWarps = kThreads / 32;
+constexpr int kMaxKpad = 128;      // largest supported atoms-per-residue (after padding to 4)
+constexpr int kMaxFB = 4;          // frames per CTA at most (2 bits in a list entry)
+constexpr int kPlanes = 7;         // x' y' z' | -2x' -2y' -2z' |a'|^2
+constexpr int kPlanesJ = 3, kPlanesI = 4;
+constexpr int kListCap = 5120;     // survivor list entries (a frame adds at most 4096)
+constexpr int kSlowCap = 1024;     // pairs waiting for the exact path
+constexpr int kSmemBudget = 74 * 1024;   // keeps three CTAs per SM
 constexpr float kPruneSlack = 1.00001f;
+constexpr float kErrC = 64.0f * 5.9604645e-8f;   // rounding bound of the expanded form, see fast_pair()
 
 __host__ __device__ inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
@@ -50,13 +64,12 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
     if (gid >= nf * nres_pad) return;
     int64_t f = gid / nres_pad;
     int r = (int)(gid - f * nres_pad);
-    float* sl = slots + (size_t)f * 3 * kpad * nres_pad + r;
     const size_t kstride = (size_t)nres_pad;
-    const size_t cstride = (size_t)kpad * nres_pad;
+    const size_t pstride = (size_t)kpad * nres_pad;
+    float* sl = slots + (size_t)f * kPlanes * pstride + r;
     if (r >= nres) {
-        for (int k = 0; k < kpad; k++) {
-            sl[k * kstride] = 0.f; sl[cstride + k * kstride] = 0.f; sl[2 * cstride + k * kstride] = 0.f;
-        }
+        for (int pl = 0; pl < kPlanes; pl++)
+            for (int k = 0; k < kpad; k++) sl[pl * pstride + k * kstride] = 0.f;
         sph[(size_t)f * nres_pad + r] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (f == 0) cnt[r] = 0;
         return;
@@ -69,17 +82,17 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
     const float inv = 1.0f / (float)n;
     const float cx = sx * inv, cy = sy * inv, cz = sz * inv;
     float r2max = 0.f;
-    const float x0 = x[0], y0 = x[1], z0 = x[2];
     for (int k = 0; k < kpad; k++) {
-        float px = x0, py = y0, pz = z0;
-        if (k < n) {
-            px = x[3 * k]; py = x[3 * k + 1]; pz = x[3 * k + 2];
-            float dx = px - cx, dy = py - cy, dz = pz - cz;
-            r2max = fmaxf(r2max, dx * dx + dy * dy + dz * dz);
-        }
-        sl[k * kstride] = px; sl[cstride + k * kstride] = py; sl[2 * cstride + k * kstride] = pz;
+        const int kk = k < n ? k : 0;
+        const float px = x[3 * kk] - cx, py = x[3 * kk + 1] - cy, pz = x[3 * kk + 2] - cz;
+        const float n2 = fmaf(pz, pz, fmaf(py, py, px * px));
+        r2max = fmaxf(r2max, n2);
+        float* o = sl + k * kstride;
+        o[0] = px; o[pstride] = py; o[2 * pstride] = pz;
+        o[3 * pstride] = -2.f * px; o[4 * pstride] = -2.f * py; o[5 * pstride] = -2.f * pz;
+        o[6 * pstride] = n2;
     }
-    sph[(size_t)f * nres_pad + r] = make_float4(cx, cy, cz, sqrtf(r2max));
+    sph[(size_t)f * nres_pad + r] = make_float4(cx, cy, cz, sqrtf(r2max) * 1.000001f);
     if (f == 0) cnt[r] = n;
 }
 
@@ -94,9 +107,6 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 }
 __device__ __forceinline__ void fence_mbar_init() {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() {
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
@@ -136,13 +146,16 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, u
 struct MdmatParams {
     const float4* sph;       // [nf][nres_pad]
     const int* cnt;          // [nres_pad]
+    const int* res_start;    // [nres + 1] (device copy)
+    const float* xyz;        // [nf][natoms][3] original coordinates (exact path)
     const float* box;        // [nf][9] or nullptr
+    const float* slots;      // [nf][7][kpad][nres_pad], for the plain-load debug path
     uint16_t* levels;        // [nf][stride]
     int64_t stride;          // elements between frames
     unsigned long long* counters;   // [0] near-boundary results [1] un-pruned residue pairs [2] atom pairs evaluated
-    int64_t P;
-    int64_t frame_base;      // first frame of this launch
-    int nres, nres_pad, kpad;
+    int64_t nf;              // frames of this launch
+    int natoms, nres, nres_pad, kpad;
+    int fb;                  // frames per CTA
     int symmetric;
     int x0, xres, y0, yres;  // block mode (symmetric: x0=y0=0, xres=yres=nres)
     int tx0, ty0;            // first 64-aligned tile of the x / y residue range
@@ -151,7 +164,6 @@ struct MdmatParams {
     int maxlevel;
     int pbc;
     int use_tma;             // 0: stage tiles with plain loads (debug aid, CONAN_MDMAT_NO_TMA=1)
-    const float* slots;      // [nf][3][kpad][nres_pad], for the plain-load path
 };
 
 __device__ __forceinline__ float min_image(float d, float L) {
@@ -169,47 +181,121 @@ __device__ __forceinline__ float dist2_exact(float dx, float dy, float dz) {
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
 }
 
+// Minimum over one chunk of ICH i-atom slots against all cj atoms of residue j, expanded form.
+// aI: i-role planes (-2x', -2y', -2z', |a'|^2) of residue i; aJ: j-role planes (x', y', z') of j;
+// (Dx, Dy, Dz) = centre_j - centre_i.  Returns min over the chunk of |a - b|^2 (approximately).
 template <int ICH>
-__device__ __forceinline__ float chunk_min(const float* __restrict__ aI, const float* __restrict__ aJ,
-                                           int cstride, int a0, int cj, float m) {
-    float xi[ICH], yi[ICH], zi[ICH];
+__device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, const float* __restrict__ aJ,
+                                                int pstride, int a0, int cj, float Dx, float Dy, float Dz, float m) {
+    float ax[ICH], ay[ICH], az[ICH], mu[ICH];
 #pragma unroll
     for (int u = 0; u < ICH; u++) {
-        xi[u] = aI[(a0 + u) * kTile];
-        yi[u] = aI[cstride + (a0 + u) * kTile];
-        zi[u] = aI[2 * cstride + (a0 + u) * kTile];
+        ax[u] = aI[(a0 + u) * kTile];
+        ay[u] = aI[pstride + (a0 + u) * kTile];
+        az[u] = aI[2 * pstride + (a0 + u) * kTile];
+        mu[u] = 3.0e38f;
     }
 #pragma unroll 2
     for (int b = 0; b < cj; b++) {
-        const float xj = aJ[b * kTile], yj = aJ[cstride + b * kTile], zj = aJ[2 * cstride + b * kTile];
+        const float bx = aJ[b * kTile] + Dx, by = aJ[pstride + b * kTile] + Dy, bz = aJ[2 * pstride + b * kTile] + Dz;
+        const float nb = fmaf(bz, bz, fmaf(by, by, bx * bx));
 #pragma unroll
-        for (int u = 0; u < ICH; u++) m = fminf(m, dist2_exact(xi[u] - xj, yi[u] - yj, zi[u] - zj));
+        for (int u = 0; u < ICH; u++) mu[u] = fminf(mu[u], fmaf(az[u], bz, fmaf(ay[u], by, fmaf(ax[u], bx, nb))));
     }
+#pragma unroll
+    for (int u = 0; u < ICH; u++) m = fminf(m, mu[u] + aI[3 * pstride + (a0 + u) * kTile]);
     return m;
 }
 
+// The exact path: reference operation order on the original coordinates (with the minimum image
+// when pbc is on).  Returns the level and counts results within 2 ulp of a level boundary.
+__device__ __forceinline__ int exact_pair(const MdmatParams& prm, int64_t f, int gi, int gj, float Lx, float Ly,
+                                          float Lz, int& near) {
+    const int a0 = prm.res_start[gi], a1 = prm.res_start[gi + 1];
+    const int b0 = prm.res_start[gj], b1 = prm.res_start[gj + 1];
+    const float* x = prm.xyz + (size_t)f * prm.natoms * 3;
+    float m = prm.trunc2;
+    for (int a = a0; a < a1; a++) {
+        const float xi = x[3 * a], yi = x[3 * a + 1], zi = x[3 * a + 2];
+        for (int b = b0; b < b1; b++) {
+            float dx = xi - x[3 * b], dy = yi - x[3 * b + 1], dz = zi - x[3 * b + 2];
+            if (prm.pbc) { dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz); }
+            m = fminf(m, dist2_exact(dx, dy, dz));
+        }
+    }
+    const float r = __fsqrt_rn(m);
+    const float tq = __fmul_rn(r, prm.invlevel);
+    int c = __float2int_rn(tq);
+    c = max(0, min(c, prm.maxlevel));
+    const float frac = fabsf(tq - rintf(tq));
+    near += (fabsf(frac - 0.5f) <= tq * 2.4e-7f) ? 1 : 0;
+    return c;
+}
+
+__device__ __forceinline__ int atom_add_shared(int* addr, int v) {
+    // plain shared-memory atomic (inline PTX keeps the compiler from wrapping it in its own
+    // warp-aggregation sequence; the callers already aggregate per warp)
+    int old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(smem_u32(addr)), "r"(v) : "memory");
+    return old;
+}
+
+// One survivor item: residue pair (i, j) of the tile in frame g of the group.  Returns the level,
+// or -1 if the expanded form cannot certify it (the pair then takes the exact path).
+template <bool PBC>
+__device__ __forceinline__ int fast_pair(const MdmatParams& prm, const float* __restrict__ aIp,
+                                         const float* __restrict__ aJp, int pstride, float4 si, float4 sj,
+                                         int ci, int cj, const float* __restrict__ box) {
+    float Dx = sj.x - si.x, Dy = sj.y - si.y, Dz = sj.z - si.z;
+    if (PBC) { Dx = min_image(Dx, box[0]); Dy = min_image(Dy, box[4]); Dz = min_image(Dz, box[8]); }
+    const float rr = si.w + sj.w;
+    const float D2 = fmaf(Dz, Dz, fmaf(Dy, Dy, Dx * Dx));
+    // |computed - reference r2| <= 22 u (rr + |D|)^2 <= 44 u (rr^2 + D2); 64 u leaves margin.
+    float E = kErrC * fmaf(rr, rr, D2);
+    // the reference forms a - b before shifting by a box length: an extra u * L per component
+    if (PBC) E += 2.5e-7f * fmaxf(box[0], fmaxf(box[4], box[8])) * (rr + sqrtf(D2));
+    float m = 3.0e38f;
+    int a0 = 0;
+    while (ci - a0 > 4) { m = chunk_min_fast<8>(aIp, aJp, pstride, a0, cj, Dx, Dy, Dz, m); a0 += 8; }
+    if (ci - a0 > 0) m = chunk_min_fast<4>(aIp, aJp, pstride, a0, cj, Dx, Dy, Dz, m);
+    if (m - E >= prm.trunc2 * 1.000001f) return prm.maxlevel;   // certainly beyond trunc
+    const float mm = fmaxf(m, 0.f);
+    if (mm < 1.0e-7f) return -1;
+    const float tq = sqrtf(mm) * prm.invlevel;
+    const float c = rintf(tq);
+    // |sqrt(e) - sqrt(m)| <= E / sqrt(m) for every e in [m-E, m+E]; the level is certain when tq
+    // stays clear of the rounding boundary (x.5) by that much plus the rounding of sqrt and mul
+    const float dt = E * prm.invlevel * rsqrtf(mm) * 1.01f + tq * 4.0e-7f + 1.0e-6f;
+    if (fabsf(fabsf(tq - c) - 0.5f) > dt) return min((int)c, prm.maxlevel);
+    return -1;
+}
+
+template <bool PBC>
 __global__ void __launch_bounds__(kThreads, 3)
-mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams prm) {
+mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_constant__ CUtensorMap tmapJ,
+                  const MdmatParams prm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int kpad = prm.kpad;
-    const int cstride = kpad * kTile;                 // floats between x / y / z planes of a tile
-    float* atomsI = reinterpret_cast<float*>(smem_raw);
-    float* atomsJ = atomsI + 3 * cstride;
-    float4* sphI = reinterpret_cast<float4*>(atomsJ + 3 * cstride);
-    float4* sphJ = sphI + kTile;
-    int* cntI = reinterpret_cast<int*>(sphJ + kTile);
+    const int kpad = prm.kpad, fbmax = prm.fb;
+    const int pstride = kpad * kTile;                 // floats between planes of one frame's tile
+    float* aI = reinterpret_cast<float*>(smem_raw);                       // [fb][4][kpad][64]
+    float* aJ = aI + (size_t)fbmax * kPlanesI * pstride;                  // [fb][3][kpad][64]
+    float4* sphI = reinterpret_cast<float4*>(aJ + (size_t)fbmax * kPlanesJ * pstride);   // [fb][64]
+    float4* sphJ = sphI + fbmax * kTile;
+    float4* grpI = sphJ + fbmax * kTile;              // [64] sphere around the residue over the whole group
+    float4* grpJ = grpI + kTile;
+    int* cntI = reinterpret_cast<int*>(grpJ + kTile);
     int* cntJ = cntI + kTile;
-    uint16_t* outT = reinterpret_cast<uint16_t*>(cntJ + kTile);   // [kTile][kTile + 2]
-    constexpr int kOutStride = kTile + 2;
-    uint16_t* list = outT + kTile * kOutStride;                   // [kTile*kTile]
-    uint64_t* bar = reinterpret_cast<uint64_t*>(list + kTile * kTile);
-    int* counters = reinterpret_cast<int*>(bar + 1);              // [0] survivors, [1] boundary hits, [2] atom pairs
+    uint16_t* list = reinterpret_cast<uint16_t*>(cntJ + kTile);          // [kListCap]
+    uint16_t* slow = list + kListCap;                                     // [kSlowCap]
+    uint64_t* bar = reinterpret_cast<uint64_t*>(slow + kSlowCap);
+    int* counters = reinterpret_cast<int*>(bar + 1);   // [0] list [1] redo list [2] near [3] evals [4] survivors
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t blk = blockIdx.x;
-    const int64_t f_local = blk / prm.ntiles;
-    const int t = (int)(blk - f_local * prm.ntiles);
-    const int64_t f = prm.frame_base + f_local;
+    const int64_t grp = blk / prm.ntiles;
+    const int t = (int)(blk - grp * prm.ntiles);
+    const int64_t f0 = grp * fbmax;                                  // first frame of the group
+    const int nfb = (int)min((int64_t)fbmax, prm.nf - f0);
     int ti, tj;
     if (prm.symmetric) {
         // t enumerates tiles (ti <= tj) row-major: row ti starts at ti*ntx - ti*(ti-1)/2
@@ -224,183 +310,214 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmap, const MdmatParams pr
         ti = t / prm.nty;
         tj = t - ti * prm.nty;
     }
-    const bool diag = prm.symmetric && ti == tj;
     // Tiles are aligned to multiples of kTile in the index group's residue numbering, so TMA
     // coordinates are always tile-aligned and inside the padded tensor.
-    const int gi0 = (prm.tx0 + ti) * kTile;   // first residue of the row tile
-    const int gj0 = (prm.ty0 + tj) * kTile;
-    const int i_beg = prm.x0, i_end = prm.x0 + prm.xres;   // residue bounds [beg, end)
+    const bool diag = prm.symmetric && ti == tj;
+    const int gi0 = (prm.tx0 + ti) * kTile, gj0 = (prm.ty0 + tj) * kTile;
+    const int i_beg = prm.x0, i_end = prm.x0 + prm.xres;
     const int j_beg = prm.y0, j_end = prm.y0 + prm.yres;
+    const int nres = prm.nres, yres = prm.yres, x0 = prm.x0, y0 = prm.y0, maxlevel = prm.maxlevel;
+    const bool symmetric = prm.symmetric != 0;
+    // element index of pair (gi, gj) inside a frame row (P < 2^31 for every supported size)
+    auto pair_idx = [&](int gi, int gj) -> int {
+        return symmetric ? gi * nres - ((gi * (gi + 1)) >> 1) + (gj - gi - 1) : (gi - x0) * yres + (gj - y0);
+    };
 
     if (tid == 0) {
         mbar_init(bar, 1);
         fence_mbar_init();
-        counters[0] = 0;
-        counters[1] = 0;
-        counters[2] = 0;
+        for (int c = 0; c < 5; c++) counters[c] = 0;
     }
     __syncthreads();
     if (prm.use_tma) {
         if (tid == 0) {
-            const uint32_t tile_bytes = 3u * (uint32_t)cstride * 4u;
-            mbar_expect_tx(bar, diag ? tile_bytes : 2u * tile_bytes);
-            tma_load_4d(atomsI, &tmap, bar, gi0, 0, 0, (int)f);
-            if (!diag) tma_load_4d(atomsJ, &tmap, bar, gj0, 0, 0, (int)f);
+            const uint32_t bytes = (uint32_t)fbmax * (kPlanesI + kPlanesJ) * (uint32_t)pstride * 4u;
+            mbar_expect_tx(bar, bytes);
+            tma_load_4d(aI, &tmapI, bar, gi0, 0, kPlanesJ, (int)f0);
+            tma_load_4d(aJ, &tmapJ, bar, gj0, 0, 0, (int)f0);
         }
     } else {
-        const float* src = prm.slots + (size_t)f * 3 * kpad * prm.nres_pad;
-        for (int idx = tid; idx < 3 * cstride; idx += kThreads) {
-            const int r = idx & (kTile - 1), ck = idx >> 6;   // ck = c*kpad + k
-            atomsI[idx] = gi0 + r < prm.nres_pad ? src[(size_t)ck * prm.nres_pad + gi0 + r] : 0.f;
-            if (!diag) atomsJ[idx] = gj0 + r < prm.nres_pad ? src[(size_t)ck * prm.nres_pad + gj0 + r] : 0.f;
+        for (int g = 0; g < nfb; g++) {
+            const float* src = prm.slots + (size_t)(f0 + g) * kPlanes * kpad * prm.nres_pad;
+            for (int idx = tid; idx < kPlanesI * pstride; idx += kThreads) {
+                const int r = idx & (kTile - 1), pk = idx >> 6;   // pk = plane*kpad + k
+                aI[(size_t)g * kPlanesI * pstride + idx] = src[(size_t)(pk + kPlanesJ * kpad) * prm.nres_pad + gi0 + r];
+            }
+            for (int idx = tid; idx < kPlanesJ * pstride; idx += kThreads) {
+                const int r = idx & (kTile - 1), pk = idx >> 6;
+                aJ[(size_t)g * kPlanesJ * pstride + idx] = src[(size_t)pk * prm.nres_pad + gj0 + r];
+            }
         }
     }
-    if (tid < kTile) {
-        const int g = gi0 + tid;
-        sphI[tid] = g < prm.nres_pad ? prm.sph[(size_t)f * prm.nres_pad + g] : make_float4(0, 0, 0, 0);
-        cntI[tid] = g < prm.nres_pad ? prm.cnt[g] : 0;
-    } else if (tid < 2 * kTile) {
-        const int l = tid - kTile, g = gj0 + l;
-        sphJ[l] = g < prm.nres_pad ? prm.sph[(size_t)f * prm.nres_pad + g] : make_float4(0, 0, 0, 0);
-        cntJ[l] = g < prm.nres_pad ? prm.cnt[g] : 0;
+    // per-frame spheres, and for the plain (non-periodic) case one sphere per residue that holds it
+    // in every frame of the group, so the pruning runs once per group instead of once per frame
+    if (tid < 2 * kTile) {
+        const bool isI = tid < kTile;
+        const int l = isI ? tid : tid - kTile;
+        const int gr = (isI ? gi0 : gj0) + l;
+        float4* dst = isI ? sphI : sphJ;
+        const float4* src = prm.sph + (size_t)f0 * prm.nres_pad + gr;
+        const float4 s0 = src[0];
+        dst[l] = s0;
+        float R = s0.w;
+        for (int g = 1; g < nfb; g++) {
+            const float4 sg = src[(size_t)g * prm.nres_pad];
+            dst[g * kTile + l] = sg;
+            const float dx = sg.x - s0.x, dy = sg.y - s0.y, dz = sg.z - s0.z;
+            R = fmaxf(R, sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx))) * 1.000001f + sg.w);
+        }
+        (isI ? grpI : grpJ)[l] = make_float4(s0.x, s0.y, s0.z, R);
+        (isI ? cntI : cntJ)[l] = prm.cnt[gr];
     }
-    float Lx = 0.f, Ly = 0.f, Lz = 0.f;
-    if (prm.pbc) {
-        const float* b = prm.box + 9 * f;
-        Lx = b[0]; Ly = b[4]; Lz = b[8];
-    }
-    __syncthreads();
 
-    // ---- phase 1: bounding-sphere pruning, survivors compacted into `list` -----------------
+    // ---- fill: every pair of the tile starts at the "beyond trunc" level -------------------
     {
-        float4 sj[2];
-        sj[0] = sphJ[lane];
-        sj[1] = sphJ[lane + 32];
-        const int gj[2] = {gj0 + lane, gj0 + lane + 32};
-#pragma unroll 1
-        for (int ii = 0; ii < kTile / (kThreads / 32); ii++) {
-            const int i = warp * (kTile / (kThreads / 32)) + ii;
+        // half a warp per row: 16 lanes x 4 levels (one 8-byte store) cover the 64 columns
+        const int sub = lane >> 4, l16 = lane & 15;
+        const uint32_t fillv = (uint32_t)maxlevel * 0x00010001u;
+        const int jlo0 = max(0, j_beg - gj0), jhi = min(kTile, j_end - gj0);
+        for (int rg = warp * 2 + sub; rg < nfb * kTile; rg += 2 * kWarps) {
+            const int g = rg >> 6, i = rg & 63;
             const int gi = gi0 + i;
-            const float4 si = sphI[i];
+            if (gi < i_beg || gi >= i_end) continue;
+            const int jlo = diag ? max(jlo0, i + 1) : jlo0;
+            if (jlo >= jhi) continue;
+            uint16_t* row = prm.levels + (size_t)(f0 + g) * prm.stride + pair_idx(gi, gj0);
+            // 8-byte aligned body, scalar head and tail
+            const int mis = (int)((reinterpret_cast<uintptr_t>(row + jlo) >> 1) & 3);   // elements past alignment
+            const int head = min((4 - mis) & 3, jhi - jlo);
+            const int body0 = jlo + head;
+            const int nq = (jhi - body0) >> 2;
+            if (l16 < head) row[jlo + l16] = (uint16_t)maxlevel;
+            if (l16 < nq) *reinterpret_cast<uint2*>(row + body0 + 4 * l16) = make_uint2(fillv, fillv);
+            const int tail0 = body0 + 4 * nq;
+            if (l16 < jhi - tail0) row[tail0 + l16] = (uint16_t)maxlevel;
+        }
+    }
+    __syncthreads();   // spheres, counts and the fill are in place
+
+    bool tiles_ready = !prm.use_tma;
+
+    // ---- survivors: fast expanded form, exact redo where the level is not certain ----------
+    // The list holds residue pairs; without periodicity an entry stands for the pair in every frame
+    // of the group (items = entries x frames), with periodicity entries carry their frame.
+    auto process_list = [&]() {
+        if (!tiles_ready) { mbar_wait(bar, 0); tiles_ready = true; }
+        const int nent = counters[0];
+        const int nitems = PBC ? nent : nent * nfb;
+        int near = 0, evals = 0;
+        for (int s = tid; s < nitems; s += kThreads) {
+            int e, g;
+            if (PBC) { e = list[s]; g = e >> 13; }
+            else { const int q = s / nfb; g = s - q * nfb; e = list[q]; }
+            const int i = e & 63, j = (e >> 6) & 63;
+            const int ci = cntI[i], cj = cntJ[j];
+            evals += ci * cj;
+            int level = -1;
+            if (!PBC || !(e & 0x1000))
+                level = fast_pair<PBC>(prm, aI + (size_t)g * kPlanesI * pstride + i, aJ + (size_t)g * kPlanesJ * pstride + j,
+                                       pstride, sphI[g * kTile + i], sphJ[g * kTile + j], ci, cj,
+                                       PBC ? prm.box + 9 * (f0 + g) : nullptr);
+            if (level < 0) {
+                const int k = atom_add_shared(&counters[1], 1);
+                if (k < kSlowCap) {
+                    slow[k] = (uint16_t)((e & 0x1fff) | (g << 13));
+                    continue;
+                }
+                float Lx = 0.f, Ly = 0.f, Lz = 0.f;   // redo list full: take the exact path right here
+                if (PBC) {
+                    const float* b = prm.box + 9 * (f0 + g);
+                    Lx = b[0]; Ly = b[4]; Lz = b[8];
+                }
+                level = exact_pair(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, near);
+            }
+            if (level < maxlevel)
+                prm.levels[(size_t)(f0 + g) * prm.stride + pair_idx(gi0 + i, gj0 + j)] = (uint16_t)level;
+        }
+        __syncthreads();
+        const int nslow = min(counters[1], kSlowCap);
+        for (int s = tid; s < nslow; s += kThreads) {
+            const int e = slow[s];
+            const int i = e & 63, j = (e >> 6) & 63, g = e >> 13;
+            float Lx = 0.f, Ly = 0.f, Lz = 0.f;
+            if (PBC) {
+                const float* b = prm.box + 9 * (f0 + g);
+                Lx = b[0]; Ly = b[4]; Lz = b[8];
+            }
+            const int level = exact_pair(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, near);
+            prm.levels[(size_t)(f0 + g) * prm.stride + pair_idx(gi0 + i, gj0 + j)] = (uint16_t)level;
+        }
+        near = __reduce_add_sync(0xffffffffu, near);
+        evals = __reduce_add_sync(0xffffffffu, evals);
+        if (lane == 0 && near) atom_add_shared(&counters[2], near);
+        if (lane == 0 && evals) atom_add_shared(&counters[3], evals);
+        __syncthreads();
+        if (tid == 0) { counters[4] += nitems; counters[0] = 0; counters[1] = 0; }
+        __syncthreads();
+    };
+
+    // ---- bounding-sphere pruning, survivors compacted into the list -------------------------
+    const float half_trunc = 0.5f * prm.trunc;
+    const int npass = PBC ? nfb : 1;
+    for (int g = 0; g < npass; g++) {
+        if (PBC && counters[0] > kListCap - kTile * kTile) process_list();   // uniform: the count is stable here
+        const float4* sI = PBC ? sphI + g * kTile : grpI;
+        const float4* sJ = PBC ? sphJ + g * kTile : grpJ;
+        float Lx = 0.f, Ly = 0.f, Lz = 0.f;
+        if (PBC) {
+            const float* b = prm.box + 9 * (f0 + g);
+            Lx = b[0]; Ly = b[4]; Lz = b[8];
+        }
+        float4 sj[2];
+        float rjp[2];   // (Rj + trunc/2) * slack: the j half of the pruning distance
+        bool jok[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int j = lane + 32 * h;
+            sj[h] = sJ[j];
+            rjp[h] = (sj[h].w + half_trunc) * kPruneSlack;
+            jok[h] = gj0 + j >= j_beg && gj0 + j < j_end;
+        }
+#pragma unroll 1
+        for (int ii = 0; ii < kTile / kWarps; ii++) {
+            const int i = warp * (kTile / kWarps) + ii;
+            const float4 si = sI[i];
+            const bool iok = gi0 + i >= i_beg && gi0 + i < i_end;
+            const float rip = (si.w + half_trunc) * kPruneSlack;
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int j = lane + 32 * h;
-                const bool valid = gi >= i_beg && gi < i_end && gj[h] >= j_beg && gj[h] < j_end &&
-                                   (!prm.symmetric || gj[h] > gi);
-                bool keep = false, general = false;
-                if (valid) {
-                    float dx = si.x - sj[h].x, dy = si.y - sj[h].y, dz = si.z - sj[h].z;
+                float dx = si.x - sj[h].x, dy = si.y - sj[h].y, dz = si.z - sj[h].z;
+                bool general = false;
+                if (PBC) {
+                    // one lattice shift serves every atom pair only if the spheres stay inside half a box
                     const float rr = si.w + sj[h].w;
-                    if (prm.pbc) {
-                        // a plain (unwrapped) inner loop is exact only if no atom pair can need a shift
-                        general = !(fabsf(dx) + rr < 0.49999f * Lx && fabsf(dy) + rr < 0.49999f * Ly &&
-                                    fabsf(dz) + rr < 0.49999f * Lz);
-                        dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz);
-                    }
-                    const float d2 = dx * dx + dy * dy + dz * dz;
-                    const float T = (prm.trunc + rr) * kPruneSlack;
-                    keep = !(d2 > T * T);
-                    if (!keep) outT[i * kOutStride + j] = (uint16_t)prm.maxlevel;
+                    dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz);
+                    general = !(fabsf(dx) + rr < 0.49999f * Lx && fabsf(dy) + rr < 0.49999f * Ly &&
+                                fabsf(dz) + rr < 0.49999f * Lz);
                 }
+                const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                const float T = rip + rjp[h];
+                const bool keep = iok && jok[h] && (!diag || j > i) && !(d2 > T * T);
                 const unsigned ball = __ballot_sync(0xffffffffu, keep);
                 if (ball) {
                     int base = 0;
-                    if (lane == 0) base = atomicAdd(&counters[0], __popc(ball));
+                    if (lane == 0) base = atom_add_shared(&counters[0], __popc(ball));
                     base = __shfl_sync(0xffffffffu, base, 0);
                     if (keep)
                         list[base + __popc(ball & ((1u << lane) - 1))] =
-                            (uint16_t)(i | (j << 6) | (general ? 0x1000 : 0));
+                            (uint16_t)(i | (j << 6) | (general ? 0x1000 : 0) | (PBC ? (g << 13) : 0));
                 }
             }
         }
+        __syncthreads();
     }
-    __syncthreads();
-    if (prm.use_tma) mbar_wait(bar, 0);   // atom tiles have landed
+    process_list();
 
-    // ---- phase 2: exact minimum over atom pairs for the survivors --------------------------
-    {
-        const int nsurv = counters[0];
-        const float* aJbase = diag ? atomsI : atomsJ;
-        int near = 0, evals = 0;
-        for (int s = tid; s < nsurv; s += kThreads) {
-            const int e = list[s];
-            const int i = e & 63, j = (e >> 6) & 63;
-            const int ci = cntI[i], cj = diag ? cntI[j] : cntJ[j];
-            const float* aI = atomsI + i;
-            const float* aJ = aJbase + j;
-            float m = prm.trunc2;
-            evals += ci * cj;
-            if (!(e & 0x1000)) {
-                int a0 = 0;
-                while (ci - a0 > 4) { m = chunk_min<8>(aI, aJ, cstride, a0, cj, m); a0 += 8; }
-                if (ci - a0 > 0) m = chunk_min<4>(aI, aJ, cstride, a0, cj, m);
-            } else {
-                for (int a = 0; a < ci; a++) {
-                    const float xi = aI[a * kTile], yi = aI[cstride + a * kTile], zi = aI[2 * cstride + a * kTile];
-                    for (int b = 0; b < cj; b++) {
-                        const float dx = min_image(xi - aJ[b * kTile], Lx);
-                        const float dy = min_image(yi - aJ[cstride + b * kTile], Ly);
-                        const float dz = min_image(zi - aJ[2 * cstride + b * kTile], Lz);
-                        m = fminf(m, dist2_exact(dx, dy, dz));
-                    }
-                }
-            }
-            const float r = __fsqrt_rn(m);
-            const float tq = __fmul_rn(r, prm.invlevel);
-            int c = __float2int_rn(tq);
-            c = max(0, min(c, prm.maxlevel));
-            outT[i * kOutStride + j] = (uint16_t)c;
-            // results within 2 ulp of a level boundary (x.5) may legitimately differ from gmx
-            const float frac = fabsf(tq - rintf(tq));
-            near += (fabsf(frac - 0.5f) <= tq * 2.4e-7f) ? 1 : 0;
-        }
-        if (prm.counters) {
-            near = __reduce_add_sync(0xffffffffu, near);
-            evals = __reduce_add_sync(0xffffffffu, evals);
-            if (lane == 0 && near) atomicAdd(&counters[1], near);
-            if (lane == 0 && evals) atomicAdd(&counters[2], evals);
-        }
-    }
-    __syncthreads();
-
-    // ---- phase 3: write the tile, one warp per row ------------------------------------------
-    {
-        uint16_t* frame_out = prm.levels + (size_t)f * prm.stride;
-        for (int i = warp; i < kTile; i += kThreads / 32) {
-            const int gi = gi0 + i;
-            if (gi < i_beg) continue;
-            if (gi >= i_end) break;
-            // valid columns of this row: [jlo, jhi) in tile coordinates
-            int jlo = max(0, j_beg - gj0), jhi = min(kTile, j_end - gj0);
-            int64_t rowbase;   // element index of column gj0 in this row
-            if (prm.symmetric) {
-                if (diag) jlo = max(jlo, i + 1);
-                rowbase = (int64_t)gi * prm.nres - (int64_t)gi * (gi + 1) / 2 + (gj0 - gi - 1);
-            } else {
-                rowbase = (int64_t)(gi - prm.x0) * prm.yres + (gj0 - prm.y0);
-            }
-            if (jlo >= jhi) continue;
-            const uint16_t* src = outT + i * kOutStride;
-            uint16_t* dst = frame_out + rowbase;
-            // peel to 4-byte alignment, then 32-bit stores
-            int j = jlo;
-            if (((reinterpret_cast<uintptr_t>(dst + j)) & 3) != 0) {
-                if (lane == 0) dst[j] = src[j];
-                j++;
-            }
-            const int npair = (jhi - j) >> 1;
-            for (int q = lane; q < npair; q += 32) {
-                const int jj = j + 2 * q;
-                const uint32_t v = (uint32_t)src[jj] | ((uint32_t)src[jj + 1] << 16);
-                *reinterpret_cast<uint32_t*>(dst + jj) = v;
-            }
-            if (((jhi - j) & 1) && lane == 0) dst[jhi - 1] = src[jhi - 1];
-        }
-        if (tid == 0 && prm.counters) {
-            if (counters[1]) atomicAdd(&prm.counters[0], (unsigned long long)counters[1]);
-            if (counters[0]) atomicAdd(&prm.counters[1], (unsigned long long)counters[0]);
-            if (counters[2]) atomicAdd(&prm.counters[2], (unsigned long long)counters[2]);
-        }
+    if (tid == 0 && prm.counters) {
+        if (counters[2]) atomicAdd(&prm.counters[0], (unsigned long long)counters[2]);
+        if (counters[4]) atomicAdd(&prm.counters[1], (unsigned long long)counters[4]);
+        if (counters[3]) atomicAdd(&prm.counters[2], (unsigned long long)counters[3]);
     }
 }
 
@@ -422,20 +539,25 @@ bool make_layout(int64_t nf, int nres, int max_res_atoms, Layout* L) {
     L->off_res_start = o; o = align256(o + sizeof(int) * (size_t)(nres + 1));
     L->off_cnt = o;       o = align256(o + sizeof(int) * (size_t)L->nres_pad);
     L->off_sph = o;       o = align256(o + sizeof(float4) * (size_t)nf * L->nres_pad);
-    L->off_slots = o;     o = align256(o + sizeof(float) * (size_t)nf * 3 * L->kpad * L->nres_pad);
+    L->off_slots = o;     o = align256(o + sizeof(float) * (size_t)nf * kPlanes * L->kpad * L->nres_pad);
     L->total = o;
     return true;
 }
 
-size_t mdmat_smem_bytes(int kpad) {
+size_t mdmat_smem_bytes(int kpad, int fb) {
     size_t s = 0;
-    s += 2 * 3 * (size_t)kpad * kTile * sizeof(float);   // atom tiles
-    s += 2 * kTile * sizeof(float4);                      // spheres
-    s += 2 * kTile * sizeof(int);                         // counts
-    s += (size_t)kTile * (kTile + 2) * sizeof(uint16_t);  // output tile
-    s += (size_t)kTile * kTile * sizeof(uint16_t);        // survivor list
-    s += 8 + 4 * sizeof(int);                             // mbarrier + counters
+    s += (size_t)fb * kPlanes * kpad * kTile * sizeof(float);   // atom tiles, both roles
+    s += (size_t)(fb + 1) * 2 * kTile * sizeof(float4);         // per-frame and per-group spheres
+    s += 2 * kTile * sizeof(int);                               // counts
+    s += (size_t)(kListCap + kSlowCap) * sizeof(uint16_t);      // survivor and redo lists
+    s += 8 + 6 * sizeof(int);                                   // mbarrier + counters
     return (s + 15) & ~(size_t)15;
+}
+
+int frames_per_cta(int kpad) {
+    int fb = kMaxFB;
+    while (fb > 1 && mdmat_smem_bytes(kpad, fb) > (size_t)kSmemBudget) fb--;
+    return fb;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -530,13 +652,15 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
     EncodeTiledFn encode = get_encode_fn();
     if (!encode) return conan::fail(CONAN_ERR_CUDA, "conan_mdmat_frames: cuTensorMapEncodeTiled unavailable");
 
-    const size_t smem = mdmat_smem_bytes(L.kpad);
-    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int fb = frames_per_cta(L.kpad);
+    const size_t smem = mdmat_smem_bytes(L.kpad, fb);
+    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 
     MdmatParams prm;
-    prm.sph = d_sph; prm.cnt = d_cnt; prm.box = d_box; prm.levels = d_levels; prm.counters = d_counters;
-    prm.P = symmetric ? (int64_t)nres * (nres - 1) / 2 : (int64_t)xres * yres;
-    prm.nres = nres; prm.nres_pad = L.nres_pad; prm.kpad = L.kpad; prm.symmetric = symmetric ? 1 : 0;
+    prm.cnt = d_cnt; prm.res_start = d_res_start; prm.counters = d_counters;
+    prm.natoms = natoms; prm.nres = nres; prm.nres_pad = L.nres_pad; prm.kpad = L.kpad; prm.fb = fb;
+    prm.symmetric = symmetric ? 1 : 0;
     prm.x0 = x0; prm.xres = xres; prm.y0 = y0; prm.yres = yres;
     prm.tx0 = x0 / kTile;
     prm.ty0 = y0 / kTile;
@@ -549,38 +673,49 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
         const char* e = getenv("CONAN_MDMAT_NO_TMA");
         prm.use_tma = (e && e[0] == '1') ? 0 : 1;
     }
-    prm.slots = d_slots;
-    if (prm.P == 0) return CONAN_OK;
-    if (levels_stride < prm.P)
-        return conan::fail(CONAN_ERR_ARG, "conan_mdmat_frames: levels_stride=%lld < P=%lld", (long long)levels_stride, (long long)prm.P);
+    const int64_t P = symmetric ? (int64_t)nres * (nres - 1) / 2 : (int64_t)xres * yres;
+    if (P == 0) return CONAN_OK;
+    if (nres > 46340 || P > 2147483647ll)
+        return conan::fail(CONAN_ERR_SIZE, "conan_mdmat_frames: %d residues exceed the supported 46340 (pair index must fit 31 bits)", nres);
+    if (levels_stride < P)
+        return conan::fail(CONAN_ERR_ARG, "conan_mdmat_frames: levels_stride=%lld < P=%lld", (long long)levels_stride, (long long)P);
     prm.stride = levels_stride;
 
     // Frames per launch: the TMA frame coordinate is an int and the grid is 1-D.
     const int64_t max_blocks = 1ll << 30;
-    const int64_t frames_per_launch = max_blocks / prm.ntiles > 0 ? max_blocks / prm.ntiles : 1;
-    for (int64_t fb = 0; fb < nf; fb += frames_per_launch) {
-        const int64_t nfl = (nf - fb < frames_per_launch) ? nf - fb : frames_per_launch;
-        // The tensor map covers only this launch's frames, so coordinate 3 stays small.
-        CUtensorMap tmap;
-        cuuint64_t gdim[4] = {(cuuint64_t)L.nres_pad, (cuuint64_t)L.kpad, 3, (cuuint64_t)nfl};
+    int64_t frames_per_launch = (max_blocks / prm.ntiles) * fb;
+    if (frames_per_launch < fb) frames_per_launch = fb;
+    for (int64_t fbase = 0; fbase < nf; fbase += frames_per_launch) {
+        const int64_t nfl = (nf - fbase < frames_per_launch) ? nf - fbase : frames_per_launch;
+        // The tensor maps cover only this launch's frames, so coordinate 3 stays small.
+        CUtensorMap tmapI, tmapJ;
+        cuuint64_t gdim[4] = {(cuuint64_t)L.nres_pad, (cuuint64_t)L.kpad, (cuuint64_t)kPlanes, (cuuint64_t)nfl};
         cuuint64_t gstr[3] = {(cuuint64_t)L.nres_pad * 4, (cuuint64_t)L.kpad * L.nres_pad * 4,
-                              (cuuint64_t)3 * L.kpad * L.nres_pad * 4};
-        cuuint32_t box[4] = {(cuuint32_t)kTile, (cuuint32_t)L.kpad, 3, 1};
+                              (cuuint64_t)kPlanes * L.kpad * L.nres_pad * 4};
+        cuuint32_t boxI[4] = {(cuuint32_t)kTile, (cuuint32_t)L.kpad, (cuuint32_t)kPlanesI, (cuuint32_t)fb};
+        cuuint32_t boxJ[4] = {(cuuint32_t)kTile, (cuuint32_t)L.kpad, (cuuint32_t)kPlanesJ, (cuuint32_t)fb};
         cuuint32_t estr[4] = {1, 1, 1, 1};
-        float* base = d_slots + (size_t)fb * 3 * L.kpad * L.nres_pad;
-        CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, box, estr,
+        float* base = d_slots + (size_t)fbase * kPlanes * L.kpad * L.nres_pad;
+        CUresult cr = encode(&tmapI, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, boxI, estr,
                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (cr == CUDA_SUCCESS)
+            cr = encode(&tmapJ, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, boxJ, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (cr != CUDA_SUCCESS)
             return conan::fail(CONAN_ERR_CUDA, "conan_mdmat_frames: cuTensorMapEncodeTiled failed (%d)", (int)cr);
         MdmatParams p2 = prm;
         // frame indices inside the kernel are relative to this launch's base pointers
-        p2.sph = d_sph + (size_t)fb * L.nres_pad;
-        p2.box = d_box ? d_box + 9 * fb : nullptr;
-        p2.levels = d_levels + (size_t)fb * prm.stride;
-        p2.frame_base = 0;
-        p2.slots = d_slots + (size_t)fb * 3 * L.kpad * L.nres_pad;
-        mdmat_tile_kernel<<<(unsigned)(nfl * prm.ntiles), kThreads, smem, stream>>>(tmap, p2);
+        p2.sph = d_sph + (size_t)fbase * L.nres_pad;
+        p2.xyz = d_xyz + (size_t)fbase * natoms * 3;
+        p2.box = d_box ? d_box + 9 * fbase : nullptr;
+        p2.levels = d_levels + (size_t)fbase * prm.stride;
+        p2.slots = base;
+        p2.nf = nfl;
+        const int64_t ngroups = (nfl + fb - 1) / fb;
+        if (prm.pbc) mdmat_tile_kernel<true><<<(unsigned)(ngroups * prm.ntiles), kThreads, smem, stream>>>(tmapI, tmapJ, p2);
+        else mdmat_tile_kernel<false><<<(unsigned)(ngroups * prm.ntiles), kThreads, smem, stream>>>(tmapI, tmapJ, p2);
         CONAN_CUDA_TRY(cudaGetLastError());
     }
     return CONAN_OK;

@@ -126,7 +126,7 @@ int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int64_t nf, in
  * CONAN_MDMAT_STATIC_SCRATCH_BYTES array inside the library (resident on every GPU that loads
  * the library, until the process exits), so a call is limited to as many frames as
  *     conan_mdmat_workspace_bytes(nf, natoms, nres, max_res_atoms) <= CONAN_MDMAT_STATIC_SCRATCH_BYTES
- * allows (about 290 frames of a 1000-residue, 8-atoms-per-residue system); larger calls return
+ * allows (about 135 frames of a 1000-residue, 8-atoms-per-residue system); larger calls return
  * CONAN_ERR_SIZE and must be split.  It calls no cudaMalloc, cudaFree or other allocating routine.
  * The first call on each device looks up the array's device address; make that first call
  * before starting any stream capture.  All calls on a device share the one array, which keeps the

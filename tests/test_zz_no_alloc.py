@@ -62,7 +62,7 @@ def test_static_scratch_rejects_calls_that_do_not_fit(lib):
     from conan_b200._lib import ConanError
     xyz, res_start, _ = synth.make_trajectory(1000, 1, seed=23)
     geom = stage1.Geometry(res_start)
-    nf = 400                                   # needs ~46 MB of scratch, the array holds 32 MiB
+    nf = 400                                   # needs ~98 MB of scratch, the array holds 32 MiB
     assert stage1.mdmat_workspace_bytes(nf, geom) > stage1.STATIC_SCRATCH_BYTES
     d_xyz = torch.from_numpy(np.repeat(xyz, nf, axis=0)).cuda()
     lv = torch.zeros((nf, geom.stride), dtype=torch.uint16, device="cuda")
