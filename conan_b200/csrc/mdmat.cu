@@ -409,7 +409,8 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         for (int s = tid; s < nitems; s += kThreads) {
             int e, g;
             if (PBC) { e = list[s]; g = e >> 13; }
-            else { const int q = s / nfb; g = s - q * nfb; e = list[q]; }
+            else { g = s / nent; e = list[s - g * nent]; }   // frame-major: a warp's lanes share the frame, so
+                                                            // their tile reads fall into different banks
             const int i = e & 63, j = (e >> 6) & 63;
             const int ci = cntI[i], cj = cntJ[j];
             evals += ci * cj;
