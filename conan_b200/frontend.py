@@ -1,0 +1,712 @@
+"""The reference's surface for the trajectory contact path, on top of the CUDA stages.
+
+`./conan.py input.inp` reads the same keyword file as the reference (conan.py:1496-1713), runs
+stage 1 in-process on the GPU where the reference shells out to `gmx mdmat` (conan.py:1437-1453),
+and `read_process_frames` returns the same tuple (conan.py:1021/1023) and writes the same files,
+with the per-frame work done by conan_pair_stats instead of Python loops.
+
+Differences a user can observe (documented in DESIGN.md): pairs_list is ordered by residue pair
+instead of by the hash order of first appearance (every consumer goes through pairs_legend);
+dmf.xpm is still written after stage 1 unless WRITE_XPM no is given or the stack is very large.
+"""
+import os
+import shutil
+import sys
+
+import numpy as np
+
+from . import levels as lv
+from . import tables, topology, xpm
+from ._lib import ConanError
+
+# ------------------------------------------------------------------------------------------------
+# keyword file
+# ------------------------------------------------------------------------------------------------
+DEFAULT_OPTS = {
+    'trunc': None, 'mean': True, 'run_mdmat': True, 'nterm': 1, 'matrices': True, 'dr_mode': 0,
+    'trunc_lifetime': 0.5, 'asymm': False, 'clean_matrices': False, 'dimer': False, 'make_movie': True,
+    'trunc_dr': None, 'trunc_inter': None, 'trunc_inter_high': None, 'domains': 0, 'begin': None, 'dt': None,
+    'end': None, 'patch_time': False, 'economy': False, 'pearson_inter': False, 'reread': False, 'indexf': None,
+    'zoom': False, 'nlevels': None,
+}
+
+_YES = lambda v: v == 'yes'
+_NOT_NO = lambda v: v != 'no'
+# keyword -> (option key, converter); the irregular ones are handled in read_options
+_SIMPLE = {
+    'TRAJ': ('traj', str), 'COORD': ('coord', str), 'NLEVEL': ('nlevels', int), 'PATCH_TIME': ('patch_time', _YES),
+    'MEAN': ('mean', _YES), 'INDEX': ('indexf', str), 'BEGIN': ('begin', int), 'END': ('end', int), 'DT': ('dt', int),
+    'TRUNC_INTER': ('trunc_inter', float), 'TRUNC_INTER_HIGH': ('trunc_inter_high', float),
+    'TRUNC_LIFETIME': ('trunc_lifetime', float), 'TRUNC_DR': ('trunc_dr', float), 'GNUS_PATH': ('gnus_path', str),
+    'RUN_MDMAT': ('run_mdmat', _YES), 'MATRICES': ('matrices', _YES), 'CLEAN_MATRICES': ('clean_matrices', _YES),
+    'PEARSON_TIME': ('pearson_time', _YES), 'PEARSON_INTER': ('pearson_inter', _YES), 'PCA_READ': ('pca_dir', str),
+    'PEARSON_OBS': ('pearson_obs_str', str), 'REREAD': ('reread', str), 'MAKE_MOVIE': ('make_movie', _NOT_NO),
+    'ECONOMY': ('economy', _NOT_NO), 'DIMER': ('dimer', _YES), 'WRITE_XPM': ('write_xpm', _NOT_NO),
+    'PBC': ('pbc', _NOT_NO), 'GROUP': ('group', int),
+}
+
+
+def parse_numbers(vals):
+    """'1 3-5 8' -> [1, 3, 4, 5, 8] (conan.py:1347-1362)."""
+    out = set()
+    toks = vals.replace("-", " - ").split()
+    last, i = 0, 0
+    while i < len(toks):
+        if toks[i] == '-':
+            if i + 1 < len(toks):
+                out |= set(range(last + 1, int(toks[i + 1]) + 1))
+                i += 1
+        else:
+            last = int(toks[i])
+            out.add(last)
+        i += 1
+    return list(out)
+
+
+def read_zoom_list(zoomfile):
+    pairs = []
+    for line in zoomfile:
+        f = line.split()
+        if f and not line.startswith("#"):
+            pairs.append(tuple(sorted((int(f[0]), int(f[1])))))
+    return pairs
+
+
+def read_stages(stagef):
+    stages = []
+    for line in stagef:
+        f = line.split()
+        if not f or line.startswith("#"):
+            continue
+        name = line[line.find('"') + 1:line.rfind('"')] if len(f) > 2 else "Stage %d" % (len(stages) + 1)
+        stages.append((int(f[0]), int(f[1]), name))
+    return stages
+
+
+def read_options(finput, opts):
+    """Keyword file -> opts dict, keys and messages as the reference (conan.py:1496-1713)."""
+    opts['trunc_given'] = False
+    for line in finput:
+        f = line.split()
+        if line.strip().startswith('#') or len(f) < 2:
+            continue
+        key, val = f[0].upper(), f[1]
+        if key in _SIMPLE:
+            name, conv = _SIMPLE[key]
+            opts[name] = conv(val)
+        elif key == 'TRUNC':
+            opts['trunc'] = float(val)
+            opts['trunc_given'] = True
+        elif key == 'DR_MODE':
+            mode = {'init': 1, 'prev': 2, 'both': 3}.get(val)
+            if mode:
+                opts['dr_mode'] = mode
+        elif key == 'NTERM':
+            opts['nterm'] = opts['xterm'] = opts['yterm'] = int(val)
+        elif key in ('START_X', 'START_Y'):
+            ax = key[-1].lower()
+            opts['start_' + ax] = int(val)
+            opts.setdefault(ax + 'term', int(val))
+            opts['asymm'] = 1
+        elif key in ('NRES_X', 'NRES_Y'):
+            opts[key[-1].lower() + 'res'] = int(val)
+            opts['asymm'] = True
+        elif key in ('NTERM_X', 'NTERM_Y'):
+            opts[key[-1].lower() + 'term'] = int(val)
+            opts['asymm'] = True
+        elif key in ('LIST_X', 'LIST_Y'):
+            opts['asymm'] = 1
+            opts['list_' + key[-1].lower()] = str(val)
+        elif key == 'SHADOW_TOL':
+            opts['shadow'] = True
+            opts['shadow_tol'] = float(val)
+        elif key == 'PCA_MAKE':
+            if not val.isdigit() or int(val) < 1:
+                print("The correct call of PCA is PCA_MAKE <# PCs>, where <# PCs> is an integer defining the number of PCs to output.")
+            else:
+                opts['pca_make'] = int(val)
+        elif key == 'ZOOM_LIST':
+            opts['zoom'] = True
+            with open(str(val)) as zf:
+                opts['zoom_list'] = read_zoom_list(zf)
+        elif key == 'BLOCKING':
+            if val != 'no':
+                opts['blocking'] = True
+        elif key in ('COORD_PDB', 'COORD_PDB_X', 'COORD_PDB_Y'):
+            opts['coordpdb'] = True
+            opts[{'COORD_PDB': 'pdbf', 'COORD_PDB_X': 'pdbx', 'COORD_PDB_Y': 'pdby'}[key]] = str(val)
+        elif key == 'IGNORE_OBS_TIME':
+            if val != 'no':
+                opts['ignore_obs_time'] = True
+        elif key in ('K_RES_CLUSTERS', 'K_TRAJ_CLUSTERS'):
+            ks = parse_numbers(" ".join(f[1:]))
+            what = 'residues' if key == 'K_RES_CLUSTERS' else 'frames'
+            if ks != [0]:
+                print("Will create the following number of clusters of %s:" % what, " ".join("%i" % k for k in ks))
+            else:
+                print("Will choose the number of clusters of %s interactively." % what)
+            if key == 'K_RES_CLUSTERS':
+                opts['k_res_clusters'] = opts['ks_res'] = ks
+            else:
+                opts['k_traj_clusters'] = opts['ks_traj'] = ks
+        elif key in ('DOMAINS', 'DOMAINS_X', 'DOMAINS_Y'):
+            opts['domains'] = True
+            opts[{'DOMAINS': 'domainf', 'DOMAINS_X': 'domainf_xn', 'DOMAINS_Y': 'domainf_yn'}[key]] = str(val)
+        elif key == 'STAGES':
+            opts['stages'] = True
+            opts['stagef'] = str(val)
+        else:
+            print("Cannot understand the keyword %s given in the input file." % key)
+    if opts['asymm']:
+        if 'shadow' in opts:
+            print("Removing shadows is impossible in an asymmetric run.")
+            opts.pop('shadow')
+        if 'k_res_clusters' in opts:
+            print("Clustering residues is impossible in an asymmetric run.")
+            opts.pop('k_res_clusters')
+            opts.pop('ks_res')
+        for ax in 'xy':
+            if 'list_' + ax in opts:
+                reslist = np.atleast_1d(np.loadtxt(opts['list_' + ax], dtype=int))
+                opts[ax + 'term'] = opts.get(ax + 'term', reslist[0])
+                opts[ax + 'dict'] = {int(b): opts[ax + 'term'] + a - 1 for a, b in enumerate(reslist)}
+                opts[ax + 'res'] = len(reslist)
+                if 'start_' + ax in opts:
+                    print("You cannot give a range AND a list for the residue list. We will only use the list.")
+                    opts.pop('start_' + ax)
+            if 'start_' + ax in opts:
+                opts[ax + 'dict'] = {opts['start_' + ax] + i: opts[ax + 'term'] + i for i in range(opts[ax + 'res'])}
+    if 'pca_make' in opts and 'pca_dir' in opts:
+        print("PCA can either be performed or PC's can be read in, but not both. We will attempt reading them in.")
+        opts.pop('pca_make')
+    if 'gnus_path' not in opts:
+        print(" .gnu paths have not been given. NO PLOTS will be produced.")
+        opts['gnus_path'] = None
+    if not opts['matrices'] and opts['make_movie']:
+        print("Can't make a movie without matrices! We will turn off movie making.")
+        opts['make_movie'] = False
+    if opts['dimer']:
+        if not opts['asymm'] or not (opts.get('xterm', 0) == opts.get('yterm', 1) and opts.get('xres', 0) == opts.get('yres', 1)):
+            print("'Dimer mode' requires 1. asymmetric mode and 2. the indices of the X- and Y- residues to be identical. We will turn off the option now.")
+            opts['dimer'] = False
+    if opts['economy']:
+        for key, msg in (('zoom', "Zooming onto residues"), ('pca_make', "PCA"), ('k_traj_clusters', "Trajectory clustering"),
+                         ('pearson_time', "Pearson correlation with time"),
+                         ('pearson_obs_str', "Pearson correlation with an observable")):
+            if opts.get(key):
+                print("%s is not available in economy mode." % msg)
+                opts.pop(key)
+    return opts
+
+
+adjust_truncs = lv.adjust_truncs
+
+
+def weight_contacts(r, trunc):
+    return (trunc - r) / trunc
+
+
+def update_interaction(r, trunc_inter, trunc_inter_high, status, inter_mode):
+    """The hysteresis rule of conan.py:24-45, kept for `import conan` users; the GPU path applies it in level space."""
+    if trunc_inter == trunc_inter_high:
+        return int(r < trunc_inter)
+    if r < trunc_inter:
+        return 1
+    if r > trunc_inter_high:
+        return 0
+    if inter_mode == 1:
+        return (r - trunc_inter) / (trunc_inter_high - trunc_inter)
+    return status
+
+
+def cond_index(i, j, n):
+    return int(n * (n - 1) / 2 - (n - i) * (n - i - 1) / 2 + j - i - 1)
+
+
+def which(program):
+    found = shutil.which(program)
+    return found if found else ''
+
+
+def handle_backups():
+    """Move output directories of an earlier run to backup.N (conan.py:1097-1115)."""
+    names = ['frames', 'input', 'matrices', 'movies', 'aggregate', 'cluster_res', 'cluster_trj', 'pca', 'zoom', 'blocking']
+    present = [d for d in names if os.path.isdir(d)]
+    if not present:
+        return 0
+    n = 1
+    while os.path.isdir("backup.%i" % n):
+        n += 1
+    target = "backup.%i" % n
+    print("Moving directories containing old calculation to: %s ..." % target)
+    os.mkdir(target)
+    for d in present:
+        shutil.move(d, os.path.join(target, d))
+    return 1
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 1
+# ------------------------------------------------------------------------------------------------
+class Stage1Result:
+    """What `gmx mdmat` would have left in dmf.xpm, kept on the GPU: full nres x nres geometry."""
+
+    def __init__(self, levels, geom, times, trunc, nlevels, n_boundary):
+        self.levels, self.geom, self.times = levels, geom, np.asarray(times, dtype=np.float64)
+        self.trunc, self.nlevels, self.n_boundary = trunc, nlevels, n_boundary
+
+    def square_host(self):
+        """[nf, nres, nres] uint16 on the host (for dmf.xpm / matrices at small sizes)."""
+        import torch
+        flat = self.levels.view(torch.int16).cpu().numpy().view(np.uint16)[:, :self.geom.P]
+        return xpm.square_from_condensed(flat, self.geom.nres)
+
+
+_last_stage1 = None   # handed from mdmat_run to read_process_frames within one process
+XPM_WRITE_LIMIT = 2.0e8   # level entries above which dmf.xpm is not written unless WRITE_XPM yes
+
+
+def select_frames(times, begin, end, dt):
+    """The -b / -e / -dt frame filter of gmx (first frame defines the dt phase)."""
+    times = np.asarray(times, dtype=np.float64)
+    keep = np.ones(len(times), dtype=bool)
+    if begin:
+        keep &= times >= begin
+    if end:
+        keep &= times <= end
+    if dt:
+        t0 = times[0] if len(times) else 0.0
+        keep &= np.abs(np.mod(times - t0 + 0.5 * 1e-3, dt)) < 1e-3 * 2
+    return np.flatnonzero(keep)
+
+
+def choose_group(groups, stdin=None, preset=None):
+    """gmx asks for the index group on stdin (the reference's tests send "2": Protein-H)."""
+    if preset is not None:
+        return preset
+    for n, (name, idx) in enumerate(groups):
+        print("Group %5d (%15s) has %5d elements" % (n, name, len(idx)))
+    print("Select a group: ", end="", flush=True)
+    line = (stdin or sys.stdin).readline()
+    if not line.strip():
+        print("")
+        raise SystemExit("No index group given on standard input.")
+    tok = line.split()[0]
+    if tok.isdigit():
+        return int(tok)
+    for n, (name, _) in enumerate(groups):
+        if name == tok:
+            return n
+    raise SystemExit("Unknown index group %s" % tok)
+
+
+def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf, pbc=True, group=None,
+              write_xpm=None, device="cuda"):
+    """Stage 1 in-process: the work of `gmx mdmat -frames` (conan.py:1437-1453).  `program` is ignored."""
+    global _last_stage1
+    import torch
+    from . import stage1
+    from .xtc import XtcFile
+    if not traj.lower().endswith(".xtc"):
+        print("Only .xtc trajectories can be read without GROMACS; got %s" % traj)
+        sys.exit()
+    nlevels = nlevels if nlevels else 40          # gmx mdmat defaults: -nlevels 40, -t 1.5
+    trunc = trunc if trunc else 1.5
+    top = topology.read_topology(coord)
+    x = XtcFile(traj)
+    if x.natoms < top.natoms:
+        top = top.truncated(x.natoms)
+    elif x.natoms > top.natoms:
+        print("The trajectory has %d atoms but %s describes only %d." % (x.natoms, coord, top.natoms))
+        sys.exit()
+    groups = topology.read_ndx(indexf) if indexf else top.default_groups()
+    gsel = choose_group(groups, preset=group)
+    name, sel = groups[gsel]
+    print("Selected %d: '%s' (%d atoms)" % (gsel, name, len(sel)))
+    res_start = top.residue_runs(sel)
+    frames = select_frames(x.times, begin, end, dt)
+    if len(frames) == 0:
+        print("No frames selected from %s." % traj)
+        sys.exit()
+    boxes = x.boxes[frames]
+    triclinic = np.abs(boxes - boxes * np.eye(3)[None]).max() > 1e-6
+    use_pbc = bool(pbc) and boxes[:, [0, 1, 2], [0, 1, 2]].min() > 0
+    if use_pbc and triclinic:
+        print("Triclinic boxes are not supported by the minimum-image code; distances are computed without PBC.")
+        use_pbc = False
+    geom = stage1.Geometry(res_start)
+    dev = torch.device(device)
+    levels = torch.zeros((len(frames), geom.stride), dtype=torch.uint16, device=dev)
+    counters = torch.zeros(3, dtype=torch.int64, device=dev)
+    batch = max(1, min(len(frames), 2048))
+    work = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
+    pinned = torch.empty((batch, geom.natoms, 3), dtype=torch.float32).pin_memory()
+    for b0 in range(0, len(frames), batch):
+        ids = frames[b0:b0 + batch]
+        x.decode(frame_ids=ids, atom_sel=sel, out=pinned.numpy()[:len(ids)])
+        d_xyz = pinned[:len(ids)].to(dev, non_blocking=True)
+        d_box = torch.from_numpy(np.ascontiguousarray(boxes[b0:b0 + batch]).reshape(-1, 9)).to(dev) if use_pbc else None
+        stage1.mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, use_pbc, levels[b0:b0 + len(ids)], work, counters)
+        torch.cuda.synchronize(dev)      # the pinned buffer is reused by the next batch
+    nb = int(counters[0].item())
+    print("Computed %d distance matrices of %d residues (%d results within 2 ulp of a level boundary)."
+          % (len(frames), geom.nres, nb))
+    _last_stage1 = Stage1Result(levels, geom, x.times[frames], trunc, nlevels, nb)
+    entries = float(len(frames)) * geom.nres * geom.nres
+    if write_xpm is None:
+        write_xpm = entries <= XPM_WRITE_LIMIT
+    if write_xpm:
+        with open("dmf.xpm", "w") as f:
+            xpm.write_xpm(f, _last_stage1.square_host(), _last_stage1.times, trunc, nlevels)
+    else:
+        print("dmf.xpm not written (%.3g entries); the level stack stays on the GPU." % entries)
+    return _last_stage1
+
+
+# ------------------------------------------------------------------------------------------------
+# xpm reading (file contract; used when RUN_MDMAT no)
+# ------------------------------------------------------------------------------------------------
+def read_index(inputf):
+    """Header of dmf.xpm -> nres, nlevels, nchar, dict_legend, trunc (conan.py:455-482)."""
+    line = inputf.readline()
+    while line.split()[0] != "static":
+        line = inputf.readline()
+    dims = inputf.readline()[1:-3].split()
+    nres, nlevels, nchar = int(dims[0]), int(dims[2]), int(dims[3])
+    codes = []
+    for _ in range(nlevels):
+        line = inputf.readline()
+        code = line[1:].split()[0]
+        codes.append(code)
+        if len(code) != nchar:
+            print('warning! this character is of the wrong length:', code)
+            print('carrying on but it is a good idea to check.')
+    trunc = float(line.split()[-2][1:-1])
+    dict_legend = dict(zip(codes, lv.legend_values(trunc, nlevels)))
+    return nres, nlevels, nchar, dict_legend, trunc
+
+
+def _levels_from_xpm(path, asymm_data):
+    """Parse dmf.xpm into (times, level stack [nf, P] uint16, layout pieces)."""
+    times, frames, trunc, nlevels = xpm.read_xpm(path)
+    nres = frames.shape[1]
+    if asymm_data:
+        xdict, ydict, xres, yres, xterm, yterm = asymm_data
+        xs = np.array([m for m in range(1, nres + 1) if m in xdict], dtype=int)
+        ys = np.array([m for m in range(1, nres + 1) if m in ydict], dtype=int)
+        # frames[f, y-1, x-1]; output block order is x-major over the residue labels
+        xo = np.array([xdict[m] - xterm for m in xs])
+        yo = np.array([ydict[m] - yterm for m in ys])
+        block = np.full((len(times), xres, yres), nlevels - 1, dtype=np.uint16)
+        block[:, xo[:, None], yo[None, :]] = frames[:, (ys - 1)[None, :], (xs - 1)[:, None]]
+        return times, block.reshape(len(times), -1), trunc, nlevels, nres
+    iu = np.triu_indices(nres, 1)
+    return times, np.ascontiguousarray(frames[:, iu[1], iu[0]]), trunc, nlevels, nres
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 2
+# ------------------------------------------------------------------------------------------------
+class Stage2Result:
+    """Everything read_process_frames derived, kept for the analyses that follow it."""
+    pass
+
+
+_last_stage2 = None
+
+
+def write_matrix(outputf, time, xterm, xres, yterm, yres, trunc, dict_frame, dr, asymm):
+    """One matrices/NNNNN.dat from a sparse frame dictionary (conan.py:570-597), for `import conan` users."""
+    if not dr:
+        outputf.write("# i  j   r_ij\n# r_ij is the shortest distance between any atom of residues  i, j.\n")
+        default = trunc
+    else:
+        outputf.write("# i  j   dr_ij\n# dr_ij is the change (compared to the previous frame)\n"
+                      "# in shortest distance between any atom of residues  i, j.\n")
+        default = 0.0
+    for i in range(xterm, xterm + xres):
+        for j in range(yterm, yterm + yres):
+            if not asymm:
+                r = 0 if i == j else dict_frame.get((i, j) if i < j else (j, i), default)
+            else:
+                r = dict_frame.get((i, j), default)
+            outputf.write("%4d %4d %9.4f\n" % (i, j, r))
+        outputf.write("\n")
+
+
+def _write_matrix_files(levels_host, values, layout, trunc, dr_mode, nframes):
+    """matrices/%05d.dat (+ _dr.init / _dr.prev) straight from the level stack."""
+    lay = layout
+    prefix = [["%4d %4d " % (i + lay.xterm, j + lay.yterm) for j in range(lay.yres)] for i in range(lay.xres)]
+    head = "# i  j   r_ij\n# r_ij is the shortest distance between any atom of residues  i, j.\n"
+    head_dr = ("# i  j   dr_ij\n# dr_ij is the change (compared to the previous frame)\n"
+               "# in shortest distance between any atom of residues  i, j.\n")
+
+    def dump(path, mat, header):
+        with open(path, "w") as f:
+            f.write(header)
+            for i in range(lay.xres):
+                f.write("".join(prefix[i][j] + "%9.4f\n" % mat[i, j] for j in range(lay.yres)))
+                f.write("\n")
+
+    first = prev = None
+    for n in range(nframes):
+        mat = lay.to_matrix(values[levels_host[n]], diag=0.0)
+        dump("matrices/%05d.dat" % n, mat, head)
+        if first is not None:
+            if dr_mode in (1, 3):
+                dump("matrices/%05d_dr.init.dat" % n, mat - first, head_dr)
+            if dr_mode in (2, 3):
+                dump("matrices/%05d_dr.prev.dat" % n, mat - prev, head_dr)
+        else:
+            first = mat
+        prev = mat
+
+
+def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, trunc, trunc_inter, trunc_inter_high,
+                        begin, end, dt, patch_time, gnus_path, dr_mode, domains, pearson_inter, economy, dimer, reread,
+                        stages_list, interact_pair_dict, trunc_lifetime, matrices=True, nterm=1, device="cuda"):
+    """Stage 2 with the reference's signature and return tuple (conan.py:697-1023).
+
+    The level stack comes from mdmat_run in this process if it ran, else from the xpm file
+    `inputf`.  All per-frame arithmetic happens in conan_pair_stats on the GPU."""
+    global _last_stage2
+    import torch
+    from . import stage1, stage2
+    if reread:
+        print("REREAD is not wired to the GPU path yet; run from the trajectory or from dmf.xpm.")
+        sys.exit()
+    if dimer:
+        print("Dimer mode is not available in this implementation; continuing without it.")
+    dev = torch.device(device)
+    asymm = bool(asymm_data)
+    s1 = _last_stage1
+    if asymm:
+        xdict, ydict, xres, yres, xterm, yterm = asymm_data
+        layout = tables.Layout(xterm=xterm, xres=xres, yterm=yterm, yres=yres)
+    else:
+        layout = tables.Layout(nres=nres, nterm=nterm)
+        xres = yres = nres
+        xterm = yterm = nterm
+    if s1 is not None and s1.geom.nres == nres and s1.nlevels == nlevels:
+        times_all = s1.times
+        if asymm:
+            xs, ys = sorted(xdict), sorted(ydict)      # xpm residue numbers (1-based) of the X and Y selections
+            sq = s1.square_host()
+            full = np.full((len(times_all), xres, yres), nlevels - 1, np.uint16)
+            full[:, np.array([xdict[m] - xterm for m in xs])[:, None], np.array([ydict[m] - yterm for m in ys])[None, :]] = \
+                sq[:, np.array(xs)[:, None] - 1, np.array(ys)[None, :] - 1]
+            stack_host, d_stack = full.reshape(len(times_all), -1), None
+        else:
+            stack_host, d_stack = None, s1.levels
+    else:
+        if inputf is None:
+            print("No dmf.xpm to read and no trajectory processed.")
+            sys.exit()
+        path = inputf.name if hasattr(inputf, "name") else "dmf.xpm"
+        times_all, stack_host, _, _, _ = _levels_from_xpm(path, asymm_data)
+        d_stack = None
+    # frame filter of conan.py:782-783 (on top of what stage 1 already selected)
+    times_all = np.asarray(times_all, dtype=np.float64)
+    t_first = times_all[0]
+    if not dt:
+        dt = times_all[1] - times_all[0] if len(times_all) > 1 else float('-inf')
+        if dt > float('-inf'):
+            print("Detected dt = %i ps" % dt)
+    if not end:
+        end = float('Inf')
+    if not begin:
+        begin = t_first
+    if patch_time:
+        times_all = times_all[0] + dt * np.arange(len(times_all))
+    if dt == float('-inf'):
+        keep = np.array([0])
+    else:
+        keep = np.flatnonzero((times_all >= begin) & (times_all <= end) & (np.mod(times_all - begin, dt) == 0))
+    if len(keep) == 0:
+        print("No frames left after applying BEGIN/END/DT.")
+        sys.exit()
+    time_vec = [float(t) for t in times_all[keep]]
+    P, stride = layout.P, lv.padded_stride(layout.P)
+    if d_stack is not None:
+        if len(keep) != d_stack.shape[0]:
+            d_stack = d_stack[torch.from_numpy(keep).to(dev)].contiguous()
+    else:
+        buf = np.zeros((len(keep), stride), np.uint16)
+        buf[:, :P] = stack_host[keep]
+        d_stack = torch.from_numpy(buf.view(np.int16)).to(dev).view(torch.uint16)
+    nf = d_stack.shape[0]
+
+    values = lv.legend_values(trunc, nlevels)
+    lo, hi, eq = lv.level_thresholds(values, trunc_inter, trunc_inter_high)
+    st = stage2.pair_stats(d_stack, P, nlevels, lo, hi, eq)
+    stats = st.host()
+    tab = tables.Stage2Tables(stats, values, time_vec, trunc, layout)
+    for d in ("aggregate", "matrices"):
+        os.makedirs(d, exist_ok=True)
+    tab.write_aggregate("aggregate")
+
+    levels_host = None
+
+    def host_levels():
+        nonlocal levels_host
+        if levels_host is None:
+            levels_host = d_stack.view(torch.int16).cpu().numpy().view(np.uint16)[:, :P]
+        return levels_host
+
+    if matrices:
+        _write_matrix_files(host_levels(), values, layout, trunc, dr_mode, nf)
+    if nf == 1:
+        print("Detected a single frame. Not very dynamic, but we will plot the distances and finish.")
+        sys.exit()
+
+    # pairs_list / pairs_legend / vectors (conan.py:806-826): pairs that ever came below trunc
+    pi, pj = layout.pair_labels()
+    seen = np.flatnonzero(tab.seen)
+    pairs_list = [(int(pi[p]), int(pj[p])) for p in seen]
+    pairs_legend = {}
+    for row, pair in enumerate(pairs_list):
+        pairs_legend[pair] = row
+        if not asymm:
+            pairs_legend[pair[::-1]] = row
+    if economy:
+        vectors = np.zeros((0, 0), dtype=np.float16)
+    else:
+        lut16 = values.astype(np.float16)
+        vectors = np.ascontiguousarray(lut16[host_levels()[:, seen]].T)
+
+    if interact_pair_dict:
+        life = layout.to_matrix(tab.lifetime, diag=-1.0)
+        with open("aggregate/interaction_types.dat", "w") as f:
+            for i in range(layout.xres):
+                for j in range(layout.yres):
+                    if i == j and not asymm:
+                        continue
+                    pair = (i + xterm, j + yterm)
+                    ok = pair in interact_pair_dict and life[i, j] >= trunc_lifetime
+                    f.write("%4d %4d %i\n" % (pair[0], pair[1], interact_pair_dict[pair] if ok else 0))
+                f.write("\n")
+
+    if stages_list:
+        hl = host_levels()
+        tv = np.array(time_vec)
+        for n, (t1, t2, title) in enumerate(stages_list):
+            a, b = np.flatnonzero(tv >= t1), np.flatnonzero(tv >= t2)
+            if len(a) == 0 or len(b) == 0:
+                print("Did NOT find stage:", title)
+                continue
+            print("Found stage:", title)
+            d = layout.to_matrix(values[hl[b[0]]], 0.0) - layout.to_matrix(values[hl[a[0]]], 0.0)
+            with open("matrices/stage_%04d_dr.dat" % (n + 1), "w") as f:
+                for i in range(layout.xres):
+                    f.write("".join("%4d %4d %9.4f\n" % (i + xterm, j + yterm, d[i, j]) for j in range(layout.yres)))
+                    f.write("\n")
+
+    density_r2_metric = {}
+    if pearson_inter:
+        density_r2_metric = _pearson_inter(host_levels(), values, layout, trunc, asymm)
+
+    print("number of frames=", len(time_vec))
+    avg_d, life_d = tab.metric_dicts()
+    res = Stage2Result()
+    res.tables, res.layout, res.d_stack, res.values, res.seen = tab, layout, d_stack, values, seen
+    res.time_vec, res.nlevels, res.trunc, res.stats = time_vec, nlevels, trunc, stats
+    _last_stage2 = res
+    if not asymm:
+        return (begin, dt, time_vec, pairs_list, pairs_legend, vectors, avg_d, life_d, density_r2_metric) + tab.interact_dicts()
+    return (begin, dt, time_vec, pairs_list, pairs_legend, vectors, avg_d, life_d, density_r2_metric) + tab.interact_dicts()
+
+
+def _pearson_inter(levels_host, values, layout, trunc, asymm):
+    """Inter-residue correlation of weighted contact numbers (conan.py:669-695, :843-850, :876-887)."""
+    w = (trunc - values[levels_host]) / trunc                  # [nf, P]
+    nf = w.shape[0]
+    out = {}
+
+    def corr_table(vecs, path, term):
+        n = vecs.shape[0]
+        varying = np.array([len(set(v)) > 1 for v in vecs])
+        with np.errstate(invalid="ignore", divide="ignore"):
+            c = np.corrcoef(vecs) if n > 1 else np.ones((1, 1))
+        c = np.where(np.outer(varying, varying), c, 0.0)
+        np.fill_diagonal(c, np.where(varying, 1.0, 0.0))
+        with open(path, "w") as f:
+            for i in range(n):
+                f.write("".join("%5i %5i %15.6f\n" % (term + i, term + j, c[i, j]) for j in range(n)))
+                f.write("\n")
+        return c
+
+    if asymm:
+        m = w.reshape(nf, layout.xres, layout.yres)
+        corr_table(m.sum(axis=2).T, "aggregate/pearson_map_density.x.dat", layout.xterm)
+        corr_table(m.sum(axis=1).T, "aggregate/pearson_map_density.y.dat", layout.yterm)
+        return out
+    n = layout.nres
+    iu = np.triu_indices(n, 1)
+    res_vec = np.zeros((n, nf))
+    np.add.at(res_vec, iu[0], w.T)
+    np.add.at(res_vec, iu[1], w.T)
+    c = corr_table(res_vec, "aggregate/pearson_map_density.dat", layout.xterm)
+    for i in range(n):
+        for j in range(n):
+            if i != j:
+                out[(i, j)] = 1 - c[i, j] ** 2
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# command line
+# ------------------------------------------------------------------------------------------------
+def main(argv=None):
+    argv = sys.argv if argv is None else argv
+    print("conan_b200: B200 implementation of the CONAN contact pipeline (no gmx needed for .xtc input)")
+    opts = dict(DEFAULT_OPTS)
+    if len(argv) != 2:
+        print('Usage: You need to provide a single text file in which specify all the options for creating a matrix!')
+        sys.exit()
+    with open(argv[1]) as finput:
+        opts = read_options(finput, opts)
+    g = opts
+    asymm_data = None
+    if g['asymm']:
+        print("Asymmetric run found!")
+        asymm_data = (g['xdict'], g['ydict'], g['xres'], g['yres'], g['xterm'], g['yterm'])
+    interact_pair_dict = None
+    trunc = g['trunc']
+    trunc_input = trunc
+    handle_backups()
+    if g.get('run_mdmat', False) and not g['reread']:
+        mdmat_run('', g['traj'], g['coord'], g['nlevels'], trunc, g['mean'], g['begin'], g['end'], g['dt'], g['indexf'],
+                  pbc=g.get('pbc', True), group=g.get('group'), write_xpm=g.get('write_xpm'))
+    if _last_stage1 is not None:
+        nres, nlevels, nchar = _last_stage1.geom.nres, _last_stage1.nlevels, (1 if _last_stage1.nlevels <= 88 else 2)
+        dict_legend, trunc = None, _last_stage1.trunc
+        inputf = None
+    else:
+        with open('dmf.xpm') as f:
+            nres, nlevels, nchar, dict_legend, trunc = read_index(f)
+        inputf = open('dmf.xpm')
+    for d in ('frames', 'matrices', 'aggregate', 'movies', 'input'):
+        os.makedirs(d, exist_ok=True)
+    shutil.copy(argv[1], 'input')
+    nterm = g['nterm']
+    if trunc != trunc_input and g['trunc_given']:
+        print("Warning! Truncation threshold given is different to the original one. Will use the given one!")
+        print("Given:     %9.4f" % trunc_input)
+        print("Detected:  %9.4f" % trunc)
+        trunc = trunc_input
+    trunc_dr, trunc_inter, trunc_inter_high = adjust_truncs(trunc, g['trunc_dr'], g['trunc_inter'], g['trunc_inter_high'])
+    print("Will read in the data now...")
+    stages_list = None
+    if 'stages' in g:
+        with open(g['stagef']) as f:
+            stages_list = read_stages(f)
+    ret = read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, trunc, trunc_inter, trunc_inter_high,
+                              g['begin'], g['end'], g['dt'], g['patch_time'], g['gnus_path'], g['dr_mode'], g['domains'],
+                              g['pearson_inter'], g['economy'], g['dimer'], g['reread'], stages_list, interact_pair_dict,
+                              g['trunc_lifetime'], matrices=g['matrices'], nterm=nterm)
+    if inputf is not None:
+        inputf.close()
+    from . import analyses
+    analyses.run_all(g, ret, _last_stage2, trunc, trunc_inter, nres, nterm, asymm_data)
+    return ret
