@@ -1,0 +1,258 @@
+// Stage 3 feeders on sm_100a: the streaming Pearson sums and the operand builders of the GEMMs.
+//
+// The reference keeps `vectors`, a float16 [pairs x frames] array of legend values
+// (conan.py:731, :821-826), and runs scipy.stats.linregress once per residue pair against time
+// (:1888-1919) and against every observable (:1922-1971), np.cov for the PCA (:1983) and
+// scipy pdist for the frame-frame distances (:2063).  Here the float16 values are looked up from
+// the uint16 level stack on the fly (a table of at most 7744 entries), so `vectors` is never
+// materialised:
+//   pearson_sums_kernel   for each pair p and each of J frame weights / centred observables O_j:
+//                         T[j][p] = sum_f O_j[f] * (y_pf - c_p) and Q[p] = sum_f O_0[f] * (y_pf - c_p)^2
+//                         (O_0 is the frame mask w).  A streaming pass, 2 B per pair-frame, HBM-bound;
+//                         float32 inside a 32-frame window, float64 across windows; the shift c_p
+//                         (about the pair's mean) removes the cancellation from the moments.
+//   operand_pairs_kernel  rows = selected pairs, K = frames: centred float32 split into TF32 hi / lo
+//                         (the A = B operand of the covariance SYRK), a tiled transpose of the stack.
+//   operand_frames_kernel rows = frames, K = selected pairs: centred on the mean frame (distances
+//                         are translation invariant) and scaled by 1/norm (the operand of the
+//                         frame-frame Gram matrix), plus the squared row norms.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "common.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kVec = 4;
+constexpr int kWin = 32;
+constexpr int kMaxJ = 8;      // frame weights + observables per pass
+constexpr int kMaxLevels = 7744;
+
+__device__ __forceinline__ uint2 ld_stream(const uint16_t* p) {
+    uint2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+
+struct PearsonParams {
+    const uint16_t* levels;
+    int64_t stride, nf, P;
+    const float* lut;          // [nlevels] float16 legend values widened to float
+    int nlevels;
+    const float* obs;          // [J][nf] O_0 = frame weights (0/1), O_j = centred observables * weight
+    int J;
+    const float* shift;        // [P] c_p
+    double* T;                 // [J][P]
+    double* Q;                 // [P]
+    int64_t chunk_len;
+};
+
+template <int J>
+__global__ void __launch_bounds__(kThreads) pearson_sums_kernel(const PearsonParams prm) {
+    extern __shared__ float s_mem[];
+    float* s_lut = s_mem;                      // [nlevels]
+    float* s_obs = s_mem + prm.nlevels;        // [J][kWin]
+    const int tid = threadIdx.x;
+    for (int i = tid; i < prm.nlevels; i += kThreads) s_lut[i] = prm.lut[i];
+    const int64_t p0 = ((int64_t)blockIdx.x * kThreads + tid) * kVec;
+    const bool in_range = p0 < prm.stride;
+    const int64_t fbeg = (int64_t)blockIdx.y * prm.chunk_len;
+    const int64_t fend = min(prm.nf, fbeg + prm.chunk_len);
+    float c[kVec];
+#pragma unroll
+    for (int q = 0; q < kVec; q++) c[q] = (p0 + q < prm.P) ? prm.shift[p0 + q] : 0.f;
+    double accT[J][kVec], accQ[kVec];
+#pragma unroll
+    for (int q = 0; q < kVec; q++) {
+        accQ[q] = 0.0;
+#pragma unroll
+        for (int j = 0; j < J; j++) accT[j][q] = 0.0;
+    }
+    const uint16_t* col = prm.levels + (in_range ? p0 : 0);
+    const int maxk = prm.nlevels - 1;
+    for (int64_t fb = fbeg; fb < fend; fb += kWin) {
+        const int nblk = (int)min((int64_t)kWin, fend - fb);
+        __syncthreads();
+        for (int i = tid; i < J * kWin; i += kThreads) {
+            const int j = i / kWin, fl = i - j * kWin;
+            s_obs[i] = fl < nblk ? prm.obs[(size_t)j * prm.nf + fb + fl] : 0.f;
+        }
+        __syncthreads();
+        float wT[J][kVec], wQ[kVec];
+#pragma unroll
+        for (int q = 0; q < kVec; q++) {
+            wQ[q] = 0.f;
+#pragma unroll
+            for (int j = 0; j < J; j++) wT[j][q] = 0.f;
+        }
+#pragma unroll 4
+        for (int fl = 0; fl < nblk; fl++) {
+            const uint2 w = ld_stream(col + (fb + fl) * prm.stride);
+            const unsigned k[kVec] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
+            float o[J];
+#pragma unroll
+            for (int j = 0; j < J; j++) o[j] = s_obs[j * kWin + fl];
+#pragma unroll
+            for (int q = 0; q < kVec; q++) {
+                const float d = s_lut[min((int)k[q], maxk)] - c[q];
+                wQ[q] = fmaf(o[0] * d, d, wQ[q]);
+#pragma unroll
+                for (int j = 0; j < J; j++) wT[j][q] = fmaf(o[j], d, wT[j][q]);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < kVec; q++) {
+            accQ[q] += (double)wQ[q];
+#pragma unroll
+            for (int j = 0; j < J; j++) accT[j][q] += (double)wT[j][q];
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < kVec; q++) {
+        const int64_t p = p0 + q;
+        if (p < prm.P) {
+            atomicAdd(&prm.Q[p], accQ[q]);
+#pragma unroll
+            for (int j = 0; j < J; j++) atomicAdd(&prm.T[(size_t)j * prm.P + p], accT[j][q]);
+        }
+    }
+}
+
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+// rows = selected pairs, K = frames.  32 x 32 tiles through shared memory (a transpose of the stack).
+__global__ void operand_pairs_kernel(const uint16_t* __restrict__ levels, int64_t stride, int64_t nf,
+                                     const int* __restrict__ sel, int nsel, const float* __restrict__ lut, int nlevels,
+                                     const float* __restrict__ mean, float* __restrict__ hi, float* __restrict__ lo,
+                                     int64_t ld /* elements per output row, multiple of 32 */) {
+    __shared__ float tile[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8 threads
+    const int64_t f0 = (int64_t)blockIdx.x * 32;
+    const int r0 = blockIdx.y * 32;
+    for (int y = ty; y < 32; y += 8) {                        // y: frame inside the tile, tx: pair
+        const int64_t f = f0 + y;
+        const int r = r0 + tx;
+        float v = 0.f;
+        if (f < nf && r < nsel) v = lut[min((int)levels[f * stride + sel[r]], nlevels - 1)] - mean[r];
+        tile[y][tx] = v;
+    }
+    __syncthreads();
+    for (int y = ty; y < 32; y += 8) {                        // y: pair inside the tile, tx: frame
+        const int r = r0 + y;
+        const int64_t f = f0 + tx;
+        if (r < nsel && f < ld) {
+            const float v = f < nf ? tile[tx][y] : 0.f;
+            const float h = to_tf32(v);
+            hi[(size_t)r * ld + f] = h;
+            lo[(size_t)r * ld + f] = to_tf32(v - h);
+        }
+    }
+}
+
+// rows = frames, K = selected pairs; also the squared norm of every row (float64).
+__global__ void operand_frames_kernel(const uint16_t* __restrict__ levels, int64_t stride, int64_t nf,
+                                      const int* __restrict__ sel, int nsel, const float* __restrict__ lut, int nlevels,
+                                      const float* __restrict__ mean, float scale, float* __restrict__ hi,
+                                      float* __restrict__ lo, int64_t ld, double* __restrict__ norm2) {
+    const int64_t f = blockIdx.x;
+    double acc = 0.0;
+    for (int64_t c = threadIdx.x; c < ld; c += blockDim.x) {
+        float v = 0.f;
+        if (c < nsel) v = (lut[min((int)levels[f * stride + sel[c]], nlevels - 1)] - mean[c]) * scale;
+        const float h = to_tf32(v);
+        const float l = to_tf32(v - h);
+        hi[(size_t)f * ld + c] = h;
+        lo[(size_t)f * ld + c] = l;
+        const double e = (double)h + (double)l;               // the value the GEMM effectively uses
+        acc += e * e;
+    }
+    __shared__ double red[32];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += red[w];
+        norm2[f] = s;
+    }
+}
+
+}  // namespace
+
+extern "C" int conan_pearson_sums(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                                  const float* d_lut, int32_t nlevels, const float* d_obs, int32_t J,
+                                  const float* d_shift, double* d_T, double* d_Q, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!d_levels || !d_lut || !d_obs || !d_shift || !d_T || !d_Q)
+        return conan::fail(CONAN_ERR_ARG, "conan_pearson_sums: null pointer argument");
+    if (nf <= 0 || P <= 0 || levels_stride < P || levels_stride % kVec != 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_pearson_sums: bad sizes nf=%lld P=%lld stride=%lld", (long long)nf,
+                           (long long)P, (long long)levels_stride);
+    if ((reinterpret_cast<uintptr_t>(d_levels) & 7) != 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_pearson_sums: level rows must be 8-byte aligned");
+    if (nlevels < 2 || nlevels > kMaxLevels)
+        return conan::fail(CONAN_ERR_SIZE, "conan_pearson_sums: nlevels=%d outside [2, %d]", nlevels, kMaxLevels);
+    if (J < 1 || J > kMaxJ)
+        return conan::fail(CONAN_ERR_SIZE, "conan_pearson_sums: J=%d outside [1, %d]; split the observables", J, kMaxJ);
+    CONAN_CUDA_TRY(cudaMemsetAsync(d_T, 0, sizeof(double) * (size_t)J * P, stream));
+    CONAN_CUDA_TRY(cudaMemsetAsync(d_Q, 0, sizeof(double) * (size_t)P, stream));
+    PearsonParams prm;
+    prm.levels = d_levels; prm.stride = levels_stride; prm.nf = nf; prm.P = P; prm.lut = d_lut; prm.nlevels = nlevels;
+    prm.obs = d_obs; prm.J = J; prm.shift = d_shift; prm.T = d_T; prm.Q = d_Q;
+    const int64_t tiles = (P + kThreads * kVec - 1) / (kThreads * kVec);
+    int64_t nchunks = (148 * 16 + tiles - 1) / tiles;
+    const int64_t maxc = nf / 64 > 0 ? nf / 64 : 1;
+    if (nchunks > maxc) nchunks = maxc;
+    if (nchunks < 1) nchunks = 1;
+    if (nchunks > 65535) nchunks = 65535;
+    int64_t clen = (nf + nchunks - 1) / nchunks;
+    clen = (clen + kWin - 1) / kWin * kWin;
+    nchunks = (nf + clen - 1) / clen;
+    prm.chunk_len = clen;
+    const size_t smem = sizeof(float) * ((size_t)nlevels + (size_t)J * kWin);
+    dim3 grid((unsigned)tiles, (unsigned)nchunks);
+#define CONAN_LAUNCH_PEARSON(JJ)                                                                              \
+    case JJ:                                                                                                   \
+        CONAN_CUDA_TRY(cudaFuncSetAttribute(pearson_sums_kernel<JJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                            (int)smem));                                                       \
+        pearson_sums_kernel<JJ><<<grid, kThreads, smem, stream>>>(prm);                                        \
+        break;
+    switch (J) {
+        CONAN_LAUNCH_PEARSON(1) CONAN_LAUNCH_PEARSON(2) CONAN_LAUNCH_PEARSON(3) CONAN_LAUNCH_PEARSON(4)
+        CONAN_LAUNCH_PEARSON(5) CONAN_LAUNCH_PEARSON(6) CONAN_LAUNCH_PEARSON(7) CONAN_LAUNCH_PEARSON(8)
+    }
+#undef CONAN_LAUNCH_PEARSON
+    CONAN_CUDA_TRY(cudaGetLastError());
+    return CONAN_OK;
+}
+
+extern "C" int conan_build_operand(const uint16_t* d_levels, int64_t levels_stride, int64_t nf,
+                                   const int32_t* d_sel, int32_t nsel, const float* d_lut, int32_t nlevels,
+                                   const float* d_mean, float scale, int32_t rows_are_frames, float* d_hi,
+                                   float* d_lo, int64_t ld, double* d_norm2, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!d_levels || !d_sel || !d_lut || !d_mean || !d_hi || !d_lo)
+        return conan::fail(CONAN_ERR_ARG, "conan_build_operand: null pointer argument");
+    if (nf <= 0 || nsel <= 0 || nlevels < 2 || nlevels > kMaxLevels)
+        return conan::fail(CONAN_ERR_ARG, "conan_build_operand: bad sizes");
+    const int64_t k = rows_are_frames ? nsel : nf;
+    if (ld < k || ld % 32 != 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_build_operand: ld=%lld must be a multiple of 32 and >= %lld", (long long)ld, (long long)k);
+    if (rows_are_frames) {
+        if (!d_norm2) return conan::fail(CONAN_ERR_ARG, "conan_build_operand: frame rows need d_norm2");
+        operand_frames_kernel<<<(unsigned)nf, 256, 0, stream>>>(d_levels, levels_stride, nf, d_sel, nsel, d_lut, nlevels,
+                                                               d_mean, scale, d_hi, d_lo, ld, d_norm2);
+    } else {
+        dim3 grid((unsigned)(ld / 32), (unsigned)((nsel + 31) / 32));
+        operand_pairs_kernel<<<grid, 256, 0, stream>>>(d_levels, levels_stride, nf, d_sel, nsel, d_lut, nlevels, d_mean,
+                                                       d_hi, d_lo, ld);
+    }
+    CONAN_CUDA_TRY(cudaGetLastError());
+    return CONAN_OK;
+}

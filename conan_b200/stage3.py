@@ -1,0 +1,126 @@
+"""Stage 3 drivers: Pearson sums, covariance and frame-frame distances over the level stack.
+
+Stand where the reference calls scipy.stats.linregress per pair (conan.py:1888-1971), np.cov
+(:1983) and scipy pdist (:2063) on its float16 `vectors`.  The float16 values are looked up from
+the stack through a table (lut16), the contractions run in conan_pearson_sums (streaming) and
+conan_gemm_3xtf32 (tcgen05 tensor cores).
+"""
+import numpy as np
+import torch
+
+from . import _lib
+
+MAX_J = 8
+
+
+def lut16(values, device):
+    """float32 device table of the legend values rounded to float16, as `vectors` stores them (:825)."""
+    return torch.from_numpy(np.asarray(values, np.float64).astype(np.float16).astype(np.float32)).to(device)
+
+
+def _stream(dev):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def pearson_sums(d_stack, P, nlevels, d_lut, obs32, shift):
+    """T [J, P], Q [P] (float64, device) for float32 frame weights / centred observables obs32 [J, nf]."""
+    lib = _lib.load()
+    if not d_stack.is_cuda:
+        raise _lib.ConanError(-1, "stage 3 needs device tensors: there is no CPU fallback")
+    dev = d_stack.device
+    nf, stride = d_stack.shape
+    J = obs32.shape[0]
+    d_obs = torch.from_numpy(np.ascontiguousarray(obs32, np.float32)).to(dev)
+    d_shift = shift if torch.is_tensor(shift) else torch.from_numpy(np.ascontiguousarray(shift, np.float32)).to(dev)
+    T = torch.empty((J, P), dtype=torch.float64, device=dev)
+    Q = torch.empty(P, dtype=torch.float64, device=dev)
+    _lib.check(lib.conan_pearson_sums(d_stack.data_ptr(), stride, nf, P, d_lut.data_ptr(), nlevels, d_obs.data_ptr(), J,
+                                      d_shift.data_ptr(), T.data_ptr(), Q.data_ptr(), _stream(dev)))
+    return T, Q
+
+
+def linregress_all(d_stack, P, nlevels, d_lut, xs, shift, frame_mask=None):
+    """scipy.stats.linregress(x_k, series_p) for every pair p and every row x_k of xs [K, nf].
+
+    Returns dict of float64 arrays: r, slope, stderr [K, P], mean and var (population) of every
+    series [P].  frame_mask (bool [nf]) restricts all sums to those frames (observables that cover
+    only part of the trajectory, conan.py:70-78)."""
+    xs = np.atleast_2d(np.asarray(xs, np.float64))
+    K, nf = xs.shape
+    w = np.ones(nf) if frame_mask is None else np.asarray(frame_mask, np.float64)
+    n = w.sum()
+    xm = (xs * w).sum(axis=1) / n
+    out = {k: np.zeros((K, P)) for k in ("r", "slope", "stderr")}
+    for k0 in range(0, K, MAX_J - 1):
+        blk = xs[k0:k0 + MAX_J - 1]
+        o32 = np.concatenate([w[None], (blk - xm[k0:k0 + len(blk), None]) * w[None]]).astype(np.float32)
+        T, Q = pearson_sums(d_stack, P, nlevels, d_lut, o32, shift)
+        T, Q = T.cpu().numpy(), Q.cpu().numpy()
+        o64 = o32.astype(np.float64)
+        S = o64.sum(axis=1)                       # what the rounded centred observables really sum to
+        ssy = Q - T[0] ** 2 / n                   # sum (y - ybar)^2
+        dev_mean = T[0] / n                       # ybar - shift
+        for j in range(len(blk)):
+            sxy = T[1 + j] - S[1 + j] * dev_mean
+            sxx = (o64[1 + j] ** 2).sum() - S[1 + j] ** 2 / n
+            with np.errstate(invalid="ignore", divide="ignore"):
+                r = sxy / np.sqrt(sxx * ssy)
+                slope = sxy / sxx
+                r = np.clip(np.where(np.isfinite(r), r, 0.0), -1.0, 1.0)
+                se = np.sqrt(np.maximum((1.0 - r * r) * ssy / sxx / (n - 2), 0.0)) if n > 2 else np.zeros(P)
+            out["r"][k0 + j], out["slope"][k0 + j], out["stderr"][k0 + j] = r, np.where(np.isfinite(slope), slope, 0.0), se
+        out["var"] = np.maximum(ssy / n, 0.0)
+        shift_h = shift.cpu().numpy() if torch.is_tensor(shift) else np.asarray(shift)
+        out["mean"] = shift_h.astype(np.float64) + dev_mean
+    return out
+
+
+def build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames, scale=1.0):
+    """(hi, lo, norm2) device tensors: centred operand split for 3xTF32; rows = pairs or frames."""
+    lib = _lib.load()
+    dev = d_stack.device
+    nf, stride = d_stack.shape
+    nsel = d_sel.numel()
+    rows, k = (nf, nsel) if rows_are_frames else (nsel, nf)
+    ld = (k + 31) // 32 * 32
+    hi = torch.empty((rows, ld), dtype=torch.float32, device=dev)
+    lo = torch.empty((rows, ld), dtype=torch.float32, device=dev)
+    norm2 = torch.empty(rows, dtype=torch.float64, device=dev) if rows_are_frames else None
+    _lib.check(lib.conan_build_operand(d_stack.data_ptr(), stride, nf, d_sel.data_ptr(), nsel, d_lut.data_ptr(), nlevels,
+                                       d_mean.data_ptr(), float(scale), 1 if rows_are_frames else 0, hi.data_ptr(),
+                                       lo.data_ptr(), ld, 0 if norm2 is None else norm2.data_ptr(), _stream(dev)))
+    return hi, lo, norm2
+
+
+def gemm_3xtf32(a_hi, a_lo, b_hi, b_lo, K, epilogue=0, alpha=1.0, row_norm2=None, col_norm2=None, symmetric=False, out=None):
+    """C = epilogue(A B^T) on the tensor cores; operands [rows, ld] float32 hi / lo parts."""
+    lib = _lib.load()
+    dev = a_hi.device
+    M, ld = a_hi.shape
+    N = b_hi.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=dev)
+    p = lambda t: 0 if t is None else t.data_ptr()
+    _lib.check(lib.conan_gemm_3xtf32(a_hi.data_ptr(), a_lo.data_ptr(), M, b_hi.data_ptr(), b_lo.data_ptr(), N, K, ld,
+                                     epilogue, float(alpha), p(row_norm2), p(col_norm2), 1 if symmetric else 0,
+                                     out.data_ptr(), out.stride(0), _stream(dev)))
+    return out
+
+
+def covariance(d_stack, sel, nlevels, d_lut, mean):
+    """np.cov(vectors) for the selected pairs (rows), ddof = 1 (conan.py:1983): [nsel, nsel] float32 on the device."""
+    dev = d_stack.device
+    nf = d_stack.shape[0]
+    d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
+    d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
+    hi, lo, _ = build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames=False)
+    return gemm_3xtf32(hi, lo, hi, lo, nf, epilogue=0, alpha=1.0 / (nf - 1), symmetric=True)
+
+
+def frame_distances(d_stack, sel, nlevels, d_lut, mean, norm):
+    """Full [nf, nf] matrix of pdist(vectors.T / norm) (conan.py:2063), float32 on the device."""
+    dev = d_stack.device
+    d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
+    d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
+    hi, lo, n2 = build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
+    return gemm_3xtf32(hi, lo, hi, lo, len(sel), epilogue=1, row_norm2=n2, col_norm2=n2, symmetric=True)

@@ -209,6 +209,45 @@ int conan_shard_summary(const uint16_t* d_levels, int64_t levels_stride, int64_t
                         uint8_t* d_decided, uint8_t* d_status, void* stream);
 
 /* ------------------------------------------------------------------------------------ */
+/* Stage 3: the dense analyses over the level stack.  The float16 `vectors` array of the   */
+/* reference (conan.py:731, :821-826) is never materialised: values come from a table of  */
+/* the float16 legend values, d_lut [nlevels] (widened to float32).                       */
+/* ------------------------------------------------------------------------------------ */
+
+/* Streaming sums behind scipy.stats.linregress of every pair's series against time
+ * (conan.py:1888-1919) and against observables (conan.py:1922-1971):
+ *     T[j][p] = sum_f O[j][f] * (y_pf - shift[p]),   j = 0..J-1        (float64 out, [J][P])
+ *     Q[p]    = sum_f O[0][f] * (y_pf - shift[p])^2                    (float64 out, [P])
+ * with y_pf = d_lut[level]; O[0] is the 0/1 frame mask, O[j>0] the centred observables times the
+ * mask (all float32 [J][nf]); shift[p] ~ the pair's mean keeps the moments free of cancellation.
+ * J <= 8 per call.  r, slope and stderr follow on the host from T, Q and sum_f O[j]^2. */
+int conan_pearson_sums(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                       const float* d_lut, int32_t nlevels, const float* d_obs, int32_t J,
+                       const float* d_shift, double* d_T, double* d_Q, void* stream);
+
+/* Builds a GEMM operand from the stack, centred and split into TF32 hi / lo parts (x = hi + lo).
+ * rows_are_frames = 0: rows = the nsel selected pairs d_sel (indices into the P columns), K = frames,
+ *     x = y - d_mean[row]                       -- the operand of np.cov(vectors), conan.py:1983.
+ * rows_are_frames = 1: rows = frames, K = selected pairs, x = (y - d_mean[col]) * scale, and
+ *     d_norm2[row] = |x|^2 (float64)            -- the operand of pdist(vectors.T / norm), conan.py:2063
+ *     (centring on the mean frame leaves distances unchanged and keeps the Gram form accurate).
+ * d_hi / d_lo are [rows][ld] float32, ld a multiple of 32 >= K; the padding is written as zeros. */
+int conan_build_operand(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, const int32_t* d_sel,
+                        int32_t nsel, const float* d_lut, int32_t nlevels, const float* d_mean, float scale,
+                        int32_t rows_are_frames, float* d_hi, float* d_lo, int64_t ld, double* d_norm2,
+                        void* stream);
+
+/* C [M][N] (float32, row pitch ldc) = epilogue(A * B^T), A = a_hi + a_lo [M][ld], B = b_hi + b_lo [N][ld],
+ * as hi*hi + hi*lo + lo*hi on the tcgen05 tensor cores (3xTF32), float32 accumulation in TMEM.
+ * epilogue 0: alpha * acc                      (covariance: alpha = 1/(nf-1), conan.py:1983)
+ * epilogue 1: sqrt(max(0, row_norm2[m] + col_norm2[n] - 2 acc))   (frame-frame distance, conan.py:2063)
+ * symmetric != 0 (needs A == B): only the upper triangle of 128 x 128 tiles is computed, both halves written. */
+int conan_gemm_3xtf32(const float* d_a_hi, const float* d_a_lo, int32_t M, const float* d_b_hi,
+                      const float* d_b_lo, int32_t N, int64_t K, int64_t ld, int32_t epilogue, float alpha,
+                      const double* d_row_norm2, const double* d_col_norm2, int32_t symmetric, float* d_c,
+                      int64_t ldc, void* stream);
+
+/* ------------------------------------------------------------------------------------ */
 /* Measurement helpers (bench.py only).                                                  */
 /* ------------------------------------------------------------------------------------ */
 
