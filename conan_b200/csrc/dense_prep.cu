@@ -120,6 +120,30 @@ __global__ void __launch_bounds__(kThreads) pearson_sums_kernel(const PearsonPar
     }
 }
 
+// Smallest and largest level of every pair over the frames with mask != 0 (all frames if mask is
+// null): decides len(set(rvec)) > 1 exactly (conan.py:1902, :1949).
+__global__ void __launch_bounds__(kThreads) level_range_kernel(const uint16_t* __restrict__ levels, int64_t stride,
+                                                               int64_t nf, int64_t P, const uint8_t* __restrict__ mask,
+                                                               int64_t chunk_len, unsigned* __restrict__ kmin,
+                                                               unsigned* __restrict__ kmax) {
+    const int64_t p0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * kVec;
+    if (p0 >= stride) return;
+    const int64_t fbeg = (int64_t)blockIdx.y * chunk_len, fend = min(nf, fbeg + chunk_len);
+    unsigned mnx = 0xffffffffu, mny = 0xffffffffu, mxx = 0, mxy = 0;
+    const uint16_t* col = levels + p0;
+    for (int64_t f = fbeg; f < fend; f++) {
+        if (mask && !mask[f]) continue;
+        const uint2 w = ld_stream(col + f * stride);
+        mnx = __vminu2(mnx, w.x); mny = __vminu2(mny, w.y);
+        mxx = __vmaxu2(mxx, w.x); mxy = __vmaxu2(mxy, w.y);
+    }
+    const unsigned mn[kVec] = {mnx & 0xffffu, mnx >> 16, mny & 0xffffu, mny >> 16};
+    const unsigned mx[kVec] = {mxx & 0xffffu, mxx >> 16, mxy & 0xffffu, mxy >> 16};
+#pragma unroll
+    for (int q = 0; q < kVec; q++)
+        if (p0 + q < P) { atomicMin(&kmin[p0 + q], mn[q]); atomicMax(&kmax[p0 + q], mx[q]); }
+}
+
 __device__ __forceinline__ float to_tf32(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -253,6 +277,27 @@ extern "C" int conan_build_operand(const uint16_t* d_levels, int64_t levels_stri
         operand_pairs_kernel<<<grid, 256, 0, stream>>>(d_levels, levels_stride, nf, d_sel, nsel, d_lut, nlevels, d_mean,
                                                        d_hi, d_lo, ld);
     }
+    CONAN_CUDA_TRY(cudaGetLastError());
+    return CONAN_OK;
+}
+
+extern "C" int conan_level_range(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                                 const uint8_t* d_frame_mask, uint32_t* d_kmin, uint32_t* d_kmax, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!d_levels || !d_kmin || !d_kmax) return conan::fail(CONAN_ERR_ARG, "conan_level_range: null pointer argument");
+    if (nf <= 0 || P <= 0 || levels_stride < P || levels_stride % kVec != 0 || (reinterpret_cast<uintptr_t>(d_levels) & 7) != 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_level_range: bad sizes or alignment");
+    CONAN_CUDA_TRY(cudaMemsetAsync(d_kmin, 0xff, sizeof(uint32_t) * (size_t)P, stream));
+    CONAN_CUDA_TRY(cudaMemsetAsync(d_kmax, 0, sizeof(uint32_t) * (size_t)P, stream));
+    const int64_t tiles = (P + kThreads * kVec - 1) / (kThreads * kVec);
+    int64_t nchunks = (148 * 16 + tiles - 1) / tiles;
+    if (nchunks > nf / 64) nchunks = nf / 64;
+    if (nchunks < 1) nchunks = 1;
+    if (nchunks > 65535) nchunks = 65535;
+    const int64_t clen = (nf + nchunks - 1) / nchunks;
+    nchunks = (nf + clen - 1) / clen;
+    dim3 grid((unsigned)tiles, (unsigned)nchunks);
+    level_range_kernel<<<grid, kThreads, 0, stream>>>(d_levels, levels_stride, nf, P, d_frame_mask, clen, d_kmin, d_kmax);
     CONAN_CUDA_TRY(cudaGetLastError());
     return CONAN_OK;
 }

@@ -39,6 +39,21 @@ def pearson_sums(d_stack, P, nlevels, d_lut, obs32, shift):
     return T, Q
 
 
+def level_range(d_stack, P, frame_mask=None):
+    """(kmin, kmax) int64 host arrays over the (masked) frames (conan_level_range)."""
+    lib = _lib.load()
+    dev = d_stack.device
+    nf, stride = d_stack.shape
+    kmin = torch.empty(P, dtype=torch.int32, device=dev)
+    kmax = torch.empty(P, dtype=torch.int32, device=dev)
+    d_mask = None
+    if frame_mask is not None:
+        d_mask = torch.from_numpy(np.ascontiguousarray(frame_mask, np.uint8)).to(dev)
+    _lib.check(lib.conan_level_range(d_stack.data_ptr(), stride, nf, P, 0 if d_mask is None else d_mask.data_ptr(),
+                                     kmin.data_ptr(), kmax.data_ptr(), _stream(dev)))
+    return kmin.cpu().numpy().astype(np.int64), kmax.cpu().numpy().astype(np.int64)
+
+
 def linregress_all(d_stack, P, nlevels, d_lut, xs, shift, frame_mask=None):
     """scipy.stats.linregress(x_k, series_p) for every pair p and every row x_k of xs [K, nf].
 

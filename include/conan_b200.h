@@ -225,6 +225,12 @@ int conan_pearson_sums(const uint16_t* d_levels, int64_t levels_stride, int64_t 
                        const float* d_lut, int32_t nlevels, const float* d_obs, int32_t J,
                        const float* d_shift, double* d_T, double* d_Q, void* stream);
 
+/* Smallest and largest level of every pair over the frames with d_frame_mask[f] != 0 (NULL = all
+ * frames); uint32 [P] each.  A series is constant -- the len(set(rvec)) > 1 tests of conan.py:1902 and
+ * :1949 fail -- iff both levels map to the same float16 legend value. */
+int conan_level_range(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                      const uint8_t* d_frame_mask, uint32_t* d_kmin, uint32_t* d_kmax, void* stream);
+
 /* Builds a GEMM operand from the stack, centred and split into TF32 hi / lo parts (x = hi + lo).
  * rows_are_frames = 0: rows = the nsel selected pairs d_sel (indices into the P columns), K = frames,
  *     x = y - d_mean[row]                       -- the operand of np.cov(vectors), conan.py:1983.

@@ -90,3 +90,79 @@ def test_cases_generated_by_the_live_reference(lib, tmp_path, case):
         if key.startswith("file/matrices/"):
             got = np.loadtxt(str(tmp_path / key[len("file/"):]))
             assert np.allclose(got, c[key], atol=1.01e-4, rtol=0), key
+
+
+def _xpm_from_goldens(goldens, workdir):
+    from conan_b200 import xpm
+    with open(os.path.join(workdir, "dmf.xpm"), "w") as f:
+        xpm.write_xpm(f, goldens["levels_sym"], np.arange(11) * 100000.0, 1.0, 1001)
+
+
+def test_pearson_matches_reference_goldens(lib, goldens, tmp_path):
+    """The reference's test 2: correlation with time, between residues and with an observable."""
+    _xpm_from_goldens(goldens, str(tmp_path))
+    with open(str(tmp_path / "observable.dat"), "w") as f:
+        f.write("1\nRandom variable\n")
+        for t, v in goldens["observable"]:
+            f.write("%d\t%.3f\n" % (t, v))
+    _run_cli(str(tmp_path), "RUN_MDMAT no\nPEARSON_TIME yes\nPEARSON_INTER yes\nPEARSON_OBS observable.dat\nMATRICES no\nMAKE_MOVIE no\n")
+    for name in ("pearson_data", "pearson_data_obs_1", "pearson_map_density"):
+        got = np.loadtxt(str(tmp_path / "aggregate" / (name + ".dat")))
+        assert _close(got, goldens["2_Pearson/aggregate/%s.dat" % name]), name
+
+
+def test_pca_matches_reference_goldens(lib, goldens, tmp_path):
+    """The reference's test 6: ten principal components of the contact series."""
+    _xpm_from_goldens(goldens, str(tmp_path))
+    _run_cli(str(tmp_path), "RUN_MDMAT no\nPCA_MAKE 10\nMATRICES no\n")
+    names = ["pca_output.txt", "pca_projections.dat"] + ["pc.%d.dat" % i for i in range(1, 10)]
+    for name in names:
+        got = np.loadtxt(str(tmp_path / "pca" / name))
+        assert _close(got, goldens["6_PCA/pca/%s" % name]), name
+
+
+def test_cluster_trajectory_matches_reference_goldens(lib, goldens, tmp_path):
+    """The reference's test 3: frame-frame distances, Ward clustering into 1-3 clusters, medoids and maps."""
+    _xpm_from_goldens(goldens, str(tmp_path))
+    _run_cli(str(tmp_path), "RUN_MDMAT no\nK_TRAJ_CLUSTERS 1-3\nMATRICES no\n")
+    checked = 0
+    for key in goldens.files:
+        if key.startswith("3_ClusterTraj/"):
+            got = np.loadtxt(str(tmp_path / key[len("3_ClusterTraj/"):]))
+            assert _close(got, goldens[key]), key
+            checked += 1
+    assert checked == 16
+
+
+def test_stage3_files_of_the_live_reference_case(lib, tmp_path):
+    """Hysteresis case with two observables, PCA and clustering; expected files from the unmodified reference."""
+    from conan_b200 import xpm
+    c = np.load(os.path.join(GOLDEN, "case_hyst.npz"))
+    with open(str(tmp_path / "dmf.xpm"), "w") as f:
+        xpm.write_xpm(f, c["in/levels_full"], c["in/times"], float(c["in/trunc"]), int(c["in/nlevels"]))
+    obs = c["in/obs"]
+    with open(str(tmp_path / "obs.dat"), "w") as f:
+        f.write("%d\n" % obs.shape[1])
+        for k in range(obs.shape[1]):
+            f.write("observable %d\n" % k)
+        for t, row in zip(c["in/times"], obs):
+            f.write("%d %s\n" % (t, " ".join("%.6f" % v for v in row)))
+    _run_cli(str(tmp_path), str(c["in/keywords"]))
+    checked = 0
+    for key in c.files:
+        if not key.startswith("file/") or key.startswith(("file/matrices", "file/aggregate/timeline", "file/aggregate/mdmat",
+                                                          "file/aggregate/native", "file/aggregate/time_", "file/aggregate/local")):
+            continue
+        path = tmp_path / key[len("file/"):]
+        assert path.exists(), key
+        got, want = np.loadtxt(str(path)), c[key]
+        assert got.shape == want.shape, key
+        if "pc." in key or "pca_projections" in key:
+            tol = 2e-5 * max(1.0, np.abs(want).max())      # eigenvectors of a float32 covariance
+        elif "linkage" in key or "rmsd_interframe" in key or "assignment" in key:
+            tol = 2e-5
+        else:
+            tol = 2.0e-6
+        assert np.abs(got - want).max() <= tol, (key, np.abs(got - want).max())
+        checked += 1
+    assert checked >= 20
