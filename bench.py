@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=1250, help="frames per H2D batch of the e2e leg")
     ap.add_argument("--cpu-frames", type=int, default=48, help="frames of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stage3", action="store_true", help="skip the stage-3 (Pearson / covariance / frame-frame) leg")
+    ap.add_argument("--stage3-frames", type=int, default=50000)
     return ap.parse_args()
 
 
@@ -378,9 +380,91 @@ def run_ours(args):
                 "value": float(P) * ncpu / t_cpu, "unit": UNIT, "cores": 1, "kind": "port",
                 "sample": "first %d frames of the same %d-residue shard (%.1f s of one host core; host has %d cores); "
                           "gmx mdmat itself: unavailable on this box" % (ncpu, nres, t_cpu, os.cpu_count() or 0)}
+        if not args.no_stage3:
+            del d_xyz, levels, work1, work2
+            torch.cuda.empty_cache()
+            line["stage3"] = run_stage3(args, dev)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_stage3(args, dev):
+    """BASELINE configs[2] (300 residues x 50k frames): Pearson vs 3 observables + time, covariance of the
+    contacting pairs, and configs[4]-style frame-frame distances on a frame subset; CUDA-event timings."""
+    import torch
+    from conan_b200 import stage1, stage2, stage3, synth
+    from conan_b200.levels import legend_values, level_thresholds
+    nres, nf = 300, args.stage3_frames
+    xyz, res_start, _ = synth.make_trajectory(nres, nf, ATOMS_PER_RES, seed=3)
+    geom = stage1.Geometry(res_start)
+    levels, _ = stage1.compute_levels(xyz, None, geom, TRUNC, NLEVELS, device=dev)
+    del xyz
+    values = legend_values(TRUNC, NLEVELS)
+    lo, hi, eq = level_thresholds(values, TRUNC_INTER, TRUNC_INTER_HIGH)
+    st = stage2.pair_stats(levels, geom.P, NLEVELS, lo, hi, eq).host()
+    P = geom.P
+    seen = np.flatnonzero(st["sum_k"] < nf * (NLEVELS - 1)).astype(np.int32)
+    lut = stage3.lut16(values, dev)
+    lut_h = values.astype(np.float16)
+    shift = lut_h[np.clip(np.rint(st["sum_k"] / nf).astype(int), 0, NLEVELS - 1)].astype(np.float32)
+    rng = np.random.default_rng(0)
+    t = np.arange(nf, dtype=np.float64) * 100.0
+    obs = np.stack([np.ones(nf), t - t.mean(), rng.normal(size=nf), np.cumsum(rng.normal(size=nf))]).astype(np.float32)
+    stream = torch.cuda.current_stream(dev)
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize(dev)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            fn()
+        b.record(stream)
+        torch.cuda.synchronize(dev)
+        return a.elapsed_time(b) / reps
+
+    d_shift = torch.from_numpy(shift).to(dev)
+    d_obs = torch.from_numpy(obs).to(dev)
+    T = torch.empty((4, P), dtype=torch.float64, device=dev)
+    Q = torch.empty(P, dtype=torch.float64, device=dev)
+    from conan_b200 import _lib
+    lib = _lib.load()
+    ms_pearson = timed(lambda: _lib.check(lib.conan_pearson_sums(levels.data_ptr(), geom.stride, nf, P, lut.data_ptr(), NLEVELS,
+                                                                 d_obs.data_ptr(), 4, d_shift.data_ptr(), T.data_ptr(),
+                                                                 Q.data_ptr(), stream.cuda_stream)))
+    mean = (shift.astype(np.float64) + T[0].cpu().numpy() / nf)[seen]
+    d_sel = torch.from_numpy(seen).to(dev)
+    d_mean = torch.from_numpy(mean.astype(np.float32)).to(dev)
+    ms_prep = timed(lambda: stage3.build_operand(levels, d_sel, NLEVELS, lut, d_mean, rows_are_frames=False), reps=2)
+    hi_, lo_, _ = stage3.build_operand(levels, d_sel, NLEVELS, lut, d_mean, rows_are_frames=False)
+    cov = torch.empty((len(seen), len(seen)), dtype=torch.float32, device=dev)
+    ms_cov = timed(lambda: stage3.gemm_3xtf32(hi_, lo_, hi_, lo_, nf, alpha=1.0 / (nf - 1), symmetric=True, out=cov), reps=2)
+    del hi_, lo_, cov
+    # frame-frame distances on the first 20 000 frames (configs[4] has 20k frames)
+    nff = min(nf, 20000)
+    fh, fl, n2 = stage3.build_operand(levels[:nff], d_sel, NLEVELS, lut, d_mean, rows_are_frames=True, scale=1.0 / (nres / np.sqrt(2.0)))
+    dist_out = torch.empty((nff, nff), dtype=torch.float32, device=dev)
+    ms_ff = timed(lambda: stage3.gemm_3xtf32(fh, fl, fh, fl, len(seen), epilogue=1, row_norm2=n2, col_norm2=n2, symmetric=True,
+                                             out=dist_out), reps=2)
+    pk, kind = peaks()
+    tf32_peak = pk["bf16_tflops"] / 2.0       # dense TF32 runs at half the bf16 rate; no TF32 entry in MEASURED_PEAKS.json
+    ntile = lambda n: (n + 127) // 128
+    mma_cov = 3 * 2.0 * (ntile(len(seen)) * (ntile(len(seen)) + 1) / 2) * 128 * 128 * ((nf + 31) // 32 * 32)
+    mma_ff = 3 * 2.0 * (ntile(nff) * (ntile(nff) + 1) / 2) * 128 * 128 * ((len(seen) + 31) // 32 * 32)
+    return {
+        "workload": "C3: %d residues x %d frames, %d of %d pairs ever in contact" % (nres, nf, len(seen), P),
+        "pearson": {"ms": ms_pearson, "observables": 3, "bound": "hbm", "achieved": 2.0 * P * nf / ms_pearson / 1e6, "unit": "GB/s",
+                    "peak": pk["hbm_gbs"], "frac": 2.0 * P * nf / ms_pearson / 1e6 / pk["hbm_gbs"]},
+        "covariance": {"ms": ms_cov, "operand_ms": ms_prep, "rows": int(len(seen)), "k": nf, "bound": "tensor",
+                       "achieved": mma_cov / ms_cov / 1e9, "unit": "TFLOP/s (TF32 MMA flops issued, 3 products)",
+                       "peak": tf32_peak, "frac": mma_cov / ms_cov / 1e9 / tf32_peak,
+                       "useful_tflops": 1.0 * len(seen) * len(seen) * nf / ms_cov / 1e9,
+                       "peak_note": "half of the measured bf16 burst (%s)" % kind},
+        "frame_frame": {"ms": ms_ff, "rows": nff, "k": int(len(seen)), "bound": "tensor", "achieved": mma_ff / ms_ff / 1e9,
+                        "unit": "TFLOP/s (TF32 MMA flops issued, 3 products)", "peak": tf32_peak,
+                        "frac": mma_ff / ms_ff / 1e9 / tf32_peak, "useful_tflops": 1.0 * nff * nff * len(seen) / ms_ff / 1e9},
+    }
 
 
 def main():
