@@ -232,6 +232,32 @@ __device__ __forceinline__ int exact_pair(const MdmatParams& prm, int64_t f, int
     return c;
 }
 
+// The same for a whole warp working on one residue pair: the atom pairs are dealt out to the lanes
+// and the minimum is combined with shuffles (a minimum does not depend on the order it is taken in).
+// Every lane returns the level; lane 0 counts the near-boundary result.
+__device__ __forceinline__ int exact_pair_warp(const MdmatParams& prm, int64_t f, int gi, int gj, float Lx, float Ly,
+                                               float Lz, int lane, int& near) {
+    const int a0 = prm.res_start[gi], na = prm.res_start[gi + 1] - a0;
+    const int b0 = prm.res_start[gj], nb = prm.res_start[gj + 1] - b0;
+    const float* x = prm.xyz + (size_t)f * prm.natoms * 3;
+    float m = prm.trunc2;
+    for (int idx = lane; idx < na * nb; idx += 32) {
+        const int a = a0 + idx / nb, b = b0 + idx % nb;
+        float dx = x[3 * a] - x[3 * b], dy = x[3 * a + 1] - x[3 * b + 1], dz = x[3 * a + 2] - x[3 * b + 2];
+        if (prm.pbc) { dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz); }
+        m = fminf(m, dist2_exact(dx, dy, dz));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    const float r = __fsqrt_rn(m);
+    const float tq = __fmul_rn(r, prm.invlevel);
+    int c = __float2int_rn(tq);
+    c = max(0, min(c, prm.maxlevel));
+    const float frac = fabsf(tq - rintf(tq));
+    if (lane == 0) near += (fabsf(frac - 0.5f) <= tq * 2.4e-7f) ? 1 : 0;
+    return c;
+}
+
 __device__ __forceinline__ int atom_add_shared(int* addr, int v) {
     // plain shared-memory atomic (inline PTX keeps the compiler from wrapping it in its own
     // warp-aggregation sequence; the callers already aggregate per warp)
@@ -406,11 +432,15 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         const int nent = counters[0];
         const int nitems = PBC ? nent : nent * nfb;
         int near = 0, evals = 0;
-        for (int s = tid; s < nitems; s += kThreads) {
+        int gq = 0, qq = tid;      // frame-major walk over (frame, entry): a warp's lanes share the frame,
+                                   // so their tile reads fall into different banks
+        for (int s = tid; s < nitems; s += kThreads, qq += kThreads) {
             int e, g;
             if (PBC) { e = list[s]; g = e >> 13; }
-            else { g = s / nent; e = list[s - g * nent]; }   // frame-major: a warp's lanes share the frame, so
-                                                            // their tile reads fall into different banks
+            else {
+                while (qq >= nent) { qq -= nent; gq++; }
+                g = gq; e = list[qq];
+            }
             const int i = e & 63, j = (e >> 6) & 63;
             const int ci = cntI[i], cj = cntJ[j];
             evals += ci * cj;
@@ -437,7 +467,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         }
         __syncthreads();
         const int nslow = min(counters[1], kSlowCap);
-        for (int s = tid; s < nslow; s += kThreads) {
+        for (int s = warp; s < nslow; s += kWarps) {      // one warp per pair on the exact path
             const int e = slow[s];
             const int i = e & 63, j = (e >> 6) & 63, g = e >> 13;
             float Lx = 0.f, Ly = 0.f, Lz = 0.f;
@@ -445,8 +475,9 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 const float* b = prm.box + 9 * (f0 + g);
                 Lx = b[0]; Ly = b[4]; Lz = b[8];
             }
-            const int level = exact_pair(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, near);
-            prm.levels[(size_t)(f0 + g) * prm.stride + pair_idx(gi0 + i, gj0 + j)] = (uint16_t)level;
+            const int level = exact_pair_warp(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, lane, near);
+            if (lane == 0)
+                prm.levels[(size_t)(f0 + g) * prm.stride + pair_idx(gi0 + i, gj0 + j)] = (uint16_t)level;
         }
         near = __reduce_add_sync(0xffffffffu, near);
         evals = __reduce_add_sync(0xffffffffu, evals);
