@@ -34,7 +34,9 @@ constexpr int kThreads = 256;
 constexpr int kVec = 4;                       // pairs per thread (one 8-byte load per frame)
 constexpr int kPairsPerCta = kThreads * kVec;
 constexpr int kWin = 32;                      // frames per history window / per-frame flush block
-constexpr int kUnroll = 8;                    // loads in flight per thread
+constexpr int kStageFrames = 8;               // frames per shared-memory stage
+constexpr int kStagesS = 4;                   // stages in flight per CTA (4 x 8 frames x 2 KB = 64 KB)
+constexpr int kConsumers = kThreads;          // 8 consumer warps; one more warp feeds the stages
 constexpr int kSmallLevels = 2049;            // up to here a warp's squared-difference sum fits 32 bits
 
 // One record per (chunk, pair), struct-of-arrays in the workspace.
@@ -58,6 +60,7 @@ struct StatsParams {
     int64_t chunk_len;
     int nchunks;
     int lo_cnt, hi_first;
+    int one;                      // == 1, opaque to the compiler: k*one - kp becomes one IMAD on the FMA pipe
     const uint16_t* first_row;    // levels of global frame 0
     const uint16_t* prev_row;     // levels of the frame before local frame 0 (may be null)
     const uint8_t* status_in;     // status entering local frame 0 (may be null = off)
@@ -76,6 +79,34 @@ __device__ __forceinline__ uint2 ld_stream(const uint16_t* p) {
     return v;
 }
 
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    for (uint32_t spin = 0; spin < (1u << 26); spin++) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();   // a copy that never lands must not hang the GPU
+}
+// One frame row of the tile, global -> shared, through the bulk-copy engine (no registers involved).
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------
 // status entering every chunk
 // ------------------------------------------------------------------------------------------
@@ -84,16 +115,21 @@ __global__ void entering_status_kernel(const StatsParams prm) {
     const int b = blockIdx.y;   // boundary: the status entering chunk b (b = nchunks: after the last frame)
     const bool live = p < prm.P;
     int64_t t = min(prm.nf, (int64_t)b * prm.chunk_len) - 1;
-    int status = -1;
-    if (!live) status = 0;
-    // all lanes of a warp walk back together until each has met a decisive frame
+    int status = live ? -1 : 0;
+    // all lanes of a warp walk back together, four rows per step (independent loads), until each has
+    // met a frame outside the buffer; the most recent such frame decides
+    const uint16_t* col = prm.levels + (live ? p : 0);
     while (true) {
-        if (status < 0 && t >= 0) {
-            const int k = prm.levels[t * prm.stride + p];
-            if (k < prm.lo_cnt) status = 1;
-            else if (k >= prm.hi_first) status = 0;
-        }
-        t--;
+        int k[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) k[u] = (status < 0 && t - u >= 0) ? (int)col[(t - u) * prm.stride] : -1;
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (status < 0 && k[u] >= 0) {
+                if (k[u] < prm.lo_cnt) status = 1;
+                else if (k[u] >= prm.hi_first) status = 0;
+            }
+        t -= 4;
         if (__all_sync(0xffffffffu, status >= 0 || t < 0)) break;
     }
     if (!live) return;
@@ -130,7 +166,7 @@ template <bool WIDE>
 __device__ __forceinline__ void frame_step(unsigned wx, unsigned wy, unsigned c_lo, unsigned c_hi, unsigned valid_y,
                                            unsigned native_y, unsigned& on_x, unsigned& on_y, unsigned (&hist)[kVec],
                                            unsigned (&a1)[kVec], unsigned (&a2)[kVec], unsigned (&kp)[kVec],
-                                           const unsigned (&k0)[kVec], FramePart* slot, bool lane0) {
+                                           const unsigned (&k0)[kVec], FramePart* slot, bool lane0, int one) {
     // hysteresis for four pairs: on = below_lo | (on & ~above_hi), verdicts in bits 15 / 31
     const unsigned ge_lo_x = wx + c_lo, ge_hi_x = wx + c_hi;
     const unsigned ge_lo_y = wy + c_lo, ge_hi_y = wy + c_hi;
@@ -146,8 +182,8 @@ __device__ __forceinline__ void frame_step(unsigned wx, unsigned wy, unsigned c_
     for (int q = 0; q < kVec; q++) {
         a1[q] += k[q];
         a2[q] += k[q] * k[q];
-        const int dp = (int)k[q] - (int)kp[q];
-        const int d0 = (int)k[q] - (int)k0[q];
+        const int dp = (int)k[q] * one - (int)kp[q];     // IMAD: keeps the integer ALU free for the bit work
+        const int d0 = (int)k[q] * one - (int)k0[q];
         sp += (unsigned)(dp * dp);
         s0 += (unsigned)(d0 * d0);
         kp[q] = k[q];
@@ -169,7 +205,8 @@ __device__ __forceinline__ void frame_step(unsigned wx, unsigned wy, unsigned c_
 }
 
 template <bool MASKED, bool WIDE>
-__device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s_part)[kThreads / 32][kWin]) {
+__device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s_part)[kThreads / 32][kWin],
+                                           const uint16_t* s_rows, uint64_t* full_bar, uint64_t* empty_bar) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool lane0 = lane == 0;
     const int64_t p0 = ((int64_t)blockIdx.x * kThreads + tid) * kVec;
@@ -186,7 +223,6 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
         valid_y = ((p0 + 0 < prm.P) ? 0x80u : 0u) | ((p0 + 1 < prm.P) ? 0x8000u : 0u) |
                   ((p0 + 2 < prm.P) ? 0x800000u : 0u) | ((p0 + 3 < prm.P) ? 0x80000000u : 0u);
     }
-    const uint16_t* col = prm.levels + (in_range ? p0 : 0);
 
     // reference rows: global frame 0 and the frame before this chunk (the chunk's own first frame
     // when there is none, which makes the first squared difference vanish)
@@ -231,37 +267,35 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
         n_int[q] = 0; n_enc[q] = 0; first_f[q] = -1; last_f[q] = -1;
     }
 
-    const size_t row_bytes = (size_t)prm.stride * sizeof(uint16_t);
-    const char* rowp = reinterpret_cast<const char*>(col + fbeg * prm.stride);
-    int buf = 0;
+    // this thread's four levels of frame r of stage slot: 8 bytes at a fixed offset
+    const uint16_t* my = s_rows + tid * kVec;
+    int it = 0, buf = 0;      // it: stage iteration since the start of the chunk
     for (int64_t fb = fbeg; fb < fend; fb += kWin, buf ^= 1) {
         const int nblk = (int)min((int64_t)kWin, fend - fb);
         FramePart* slots = &s_part[buf][warp][0];
-        if (nblk == kWin) {
 #pragma unroll 1
-            for (int u0 = 0; u0 < kWin; u0 += kUnroll) {
-                uint2 w[kUnroll];
+        for (int u0 = 0; u0 < nblk; u0 += kStageFrames, it++) {
+            const int slot = it % kStagesS;
+            mbar_wait(&full_bar[slot], (uint32_t)(it / kStagesS) & 1u);
+            const uint16_t* rows = my + (size_t)slot * kStageFrames * kPairsPerCta;
+            if (nblk - u0 >= kStageFrames) {
 #pragma unroll
-                for (int u = 0; u < kUnroll; u++) {
-                    w[u] = ld_stream(reinterpret_cast<const uint16_t*>(rowp));
-                    rowp += row_bytes;
+                for (int u = 0; u < kStageFrames; u++) {
+                    uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
+                    if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
+                    frame_step<WIDE>(w.x, w.y, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
+                                     slots + u0 + u, lane0, prm.one);
                 }
-#pragma unroll
-                for (int u = 0; u < kUnroll; u++) {
-                    unsigned wx = w[u].x, wy = w[u].y;
-                    if (MASKED) { wx &= mask_x; wy &= mask_y; }
-                    frame_step<WIDE>(wx, wy, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
-                                     slots + u0 + u, lane0);
+            } else {   // the last, partial stage of the call
+                for (int u = 0; u < nblk - u0; u++) {
+                    uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
+                    if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
+                    frame_step<WIDE>(w.x, w.y, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
+                                     slots + u0 + u, lane0, prm.one);
                 }
             }
-        } else {   // the last, partial window of the call
-            for (int fl = 0; fl < nblk; fl++) {
-                uint2 w = ld_stream(reinterpret_cast<const uint16_t*>(rowp));
-                rowp += row_bytes;
-                if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
-                frame_step<WIDE>(w.x, w.y, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
-                                 slots + fl, lane0);
-            }
+            __syncwarp();
+            if (lane0) mbar_arrive(&empty_bar[slot]);      // this warp is done with the stage
         }
         // close the window: counts from the history masks, widen the 32-bit sums (nlevels <= 7744
         // keeps 32 frames of k^2 below 2^31)
@@ -274,9 +308,9 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
         carry = (hist[0] & 1u) | ((hist[1] & 1u) << 1) | ((hist[2] & 1u) << 2) | ((hist[3] & 1u) << 3);
 #pragma unroll
         for (int q = 0; q < kVec; q++) hist[q] = 0;
-        // one barrier per window: the buffers alternate, so this window's readers are done before
-        // the buffer is written again two windows later
-        __syncthreads();
+        // one barrier per window (consumer warps only): the buffers alternate, so this window's readers
+        // are done before the buffer is written again two windows later
+        asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
         if (tid < nblk) {
             unsigned cnt = 0;
             unsigned long long vp = 0, v0 = 0;
@@ -314,12 +348,41 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
 }
 
 template <bool WIDE>
-__global__ void __launch_bounds__(kThreads, 2) pair_stats_kernel(const StatsParams prm) {
+__global__ void __launch_bounds__(kThreads + 32, 2) pair_stats_kernel(const StatsParams prm) {
+    extern __shared__ __align__(128) unsigned char s_dyn[];    // [kStagesS][kStageFrames][1024] levels
     __shared__ __align__(16) FramePart s_part[2][kThreads / 32][kWin];   // per-warp, per-frame partial sums
+    __shared__ __align__(8) uint64_t full_bar[kStagesS], empty_bar[kStagesS];
+    uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_dyn);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kStagesS; i++) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], kThreads / 32); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x >= kConsumers) {
+        // ---- producer warp: one lane keeps kStagesS stages of kStageFrames rows in flight ----
+        if (threadIdx.x == kConsumers) {
+            const int64_t tile_p0 = (int64_t)blockIdx.x * kPairsPerCta;
+            const int64_t fbeg = (int64_t)blockIdx.y * prm.chunk_len;
+            const int64_t fend = min(prm.nf, fbeg + prm.chunk_len);
+            const uint32_t row_bytes = (uint32_t)min((int64_t)kPairsPerCta, prm.stride - tile_p0) * 2u;
+            const uint16_t* src = prm.levels + tile_p0;
+            int it = 0;
+            for (int64_t f = fbeg; f < fend; f += kStageFrames, it++) {
+                const int slot = it % kStagesS;
+                mbar_wait(&empty_bar[slot], ((uint32_t)(it / kStagesS) & 1u) ^ 1u);
+                const int nrows = (int)min((int64_t)kStageFrames, fend - f);
+                mbar_expect_tx(&full_bar[slot], row_bytes * (uint32_t)nrows);
+                uint16_t* dst = s_rows + (size_t)slot * kStageFrames * kPairsPerCta;
+                for (int r = 0; r < nrows; r++)
+                    bulk_load(dst + (size_t)r * kPairsPerCta, src + (f + r) * prm.stride, row_bytes, &full_bar[slot]);
+            }
+        }
+        return;
+    }
     // only the last pair tile can contain padding columns
     const bool tail = ((int64_t)(blockIdx.x + 1) * kPairsPerCta > prm.P);
-    if (tail) stats_body<true, WIDE>(prm, s_part);
-    else stats_body<false, WIDE>(prm, s_part);
+    if (tail) stats_body<true, WIDE>(prm, s_part, s_rows, full_bar, empty_bar);
+    else stats_body<false, WIDE>(prm, s_part, s_rows, full_bar, empty_bar);
 }
 
 struct CombineParams {
@@ -459,7 +522,7 @@ extern "C" int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride,
 
     StatsParams sp;
     sp.levels = d_levels; sp.stride = levels_stride; sp.nf = nf; sp.P = P; sp.frame0 = frame0;
-    sp.chunk_len = pl.chunk_len; sp.nchunks = pl.nchunks; sp.lo_cnt = lo_cnt; sp.hi_first = hi_first;
+    sp.chunk_len = pl.chunk_len; sp.nchunks = pl.nchunks; sp.lo_cnt = lo_cnt; sp.hi_first = hi_first; sp.one = 1;
     sp.first_row = d_first_row ? d_first_row : d_levels;
     sp.prev_row = d_prev_row;
     sp.status_in = d_status_in;
@@ -475,8 +538,14 @@ extern "C" int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride,
     entering_status_kernel<<<egrid, 256, 0, stream>>>(sp);
     CONAN_CUDA_TRY(cudaGetLastError());
     dim3 grid((unsigned)tiles, (unsigned)pl.nchunks);
-    if (nlevels <= kSmallLevels) pair_stats_kernel<false><<<grid, kThreads, 0, stream>>>(sp);
-    else pair_stats_kernel<true><<<grid, kThreads, 0, stream>>>(sp);
+    const size_t smem = (size_t)kStagesS * kStageFrames * kPairsPerCta * sizeof(uint16_t);
+    if (nlevels <= kSmallLevels) {
+        CONAN_CUDA_TRY(cudaFuncSetAttribute(pair_stats_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        pair_stats_kernel<false><<<grid, kThreads + 32, smem, stream>>>(sp);
+    } else {
+        CONAN_CUDA_TRY(cudaFuncSetAttribute(pair_stats_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        pair_stats_kernel<true><<<grid, kThreads + 32, smem, stream>>>(sp);
+    }
     CONAN_CUDA_TRY(cudaGetLastError());
 
     CombineParams cp;
