@@ -66,6 +66,7 @@ SIGNATURES = {
     "conan_pearson_sums": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_void_p, c_i32, c_void_p, c_i32,
                                           c_void_p, c_void_p, c_void_p, c_void_p]),
     "conan_level_range": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "conan_residue_weights": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i32, c_i32, c_i32, c_i32, c_void_p, c_void_p]),
     "conan_build_operand": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_void_p, c_i32, c_void_p, c_i32, c_void_p,
                                            c_f32, c_i32, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "conan_gemm_3xtf32": (ctypes.c_int, [c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_i32, c_i64, c_i64,

@@ -144,6 +144,37 @@ __global__ void __launch_bounds__(kThreads) level_range_kernel(const uint16_t* _
         if (p0 + q < P) { atomicMin(&kmin[p0 + q], mn[q]); atomicMax(&kmax[p0 + q], mx[q]); }
 }
 
+// Per frame and residue: sum over the residue's pairs of (maxlevel - level), i.e. the weighted number
+// of contacts (trunc - r)/trunc of conan.py:19-21, :843-850 in level units (exact integers).
+// One CTA per frame; each pair is read once and credited to both of its residues in shared memory.
+__global__ void residue_weights_kernel(const uint16_t* __restrict__ levels, int64_t stride, int symmetric, int xres,
+                                       int yres, int maxlevel, int* __restrict__ out /* [nf][xres (+ yres)] */) {
+    extern __shared__ int s_w[];
+    const int nout = symmetric ? xres : xres + yres;
+    for (int i = threadIdx.x; i < nout; i += blockDim.x) s_w[i] = 0;
+    __syncthreads();
+    const uint16_t* row = levels + (size_t)blockIdx.x * stride;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    for (int i = warp; i < xres; i += nwarp) {
+        int64_t base;
+        int j0, j1;
+        if (symmetric) { base = (int64_t)i * xres - (int64_t)i * (i + 1) / 2 - i - 1; j0 = i + 1; j1 = xres; }
+        else { base = (int64_t)i * yres; j0 = 0; j1 = yres; }
+        int acc = 0;
+        for (int j = j0 + lane; j < j1; j += 32) {
+            const int w = maxlevel - min((int)row[base + j], maxlevel);
+            if (w) {
+                acc += w;
+                atomicAdd(&s_w[symmetric ? j : xres + j], w);
+            }
+        }
+        acc = __reduce_add_sync(0xffffffffu, acc);
+        if (lane == 0 && acc) atomicAdd(&s_w[i], acc);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nout; i += blockDim.x) out[(size_t)blockIdx.x * nout + i] = s_w[i];
+}
+
 __device__ __forceinline__ float to_tf32(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -298,6 +329,25 @@ extern "C" int conan_level_range(const uint16_t* d_levels, int64_t levels_stride
     nchunks = (nf + clen - 1) / clen;
     dim3 grid((unsigned)tiles, (unsigned)nchunks);
     level_range_kernel<<<grid, kThreads, 0, stream>>>(d_levels, levels_stride, nf, P, d_frame_mask, clen, d_kmin, d_kmax);
+    CONAN_CUDA_TRY(cudaGetLastError());
+    return CONAN_OK;
+}
+
+extern "C" int conan_residue_weights(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int32_t symmetric,
+                                     int32_t xres, int32_t yres, int32_t nlevels, int32_t* d_out, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!d_levels || !d_out) return conan::fail(CONAN_ERR_ARG, "conan_residue_weights: null pointer argument");
+    if (nf <= 0 || xres <= 0 || (!symmetric && yres <= 0) || nlevels < 2 || nlevels > kMaxLevels)
+        return conan::fail(CONAN_ERR_ARG, "conan_residue_weights: bad sizes");
+    const int64_t P = symmetric ? (int64_t)xres * (xres - 1) / 2 : (int64_t)xres * yres;
+    if (levels_stride < P) return conan::fail(CONAN_ERR_ARG, "conan_residue_weights: levels_stride < P");
+    const int nout = symmetric ? xres : xres + yres;
+    if (nout > 48000 || nf > 2147483647ll)
+        return conan::fail(CONAN_ERR_SIZE, "conan_residue_weights: more than 48000 residues");
+    const size_t smem = sizeof(int) * (size_t)nout;
+    CONAN_CUDA_TRY(cudaFuncSetAttribute(residue_weights_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    residue_weights_kernel<<<(unsigned)nf, 256, smem, stream>>>(d_levels, levels_stride, symmetric ? 1 : 0, xres, yres,
+                                                               nlevels - 1, d_out);
     CONAN_CUDA_TRY(cudaGetLastError());
     return CONAN_OK;
 }

@@ -405,6 +405,98 @@ def _levels_from_xpm(path, asymm_data):
 
 
 # ------------------------------------------------------------------------------------------------
+# REREAD: matrices/NNNNN.dat of an earlier run instead of a trajectory (conan.py:745-761, :1051-1071, :1455-1494)
+# ------------------------------------------------------------------------------------------------
+def read_index_folder(reread):
+    """index.dat of a REREAD folder -> asymm, nterm, nres, trunc, asymm_keys."""
+    asymm, nterm, trunc, nres, keys = 0, 1, 1.5, None, {}
+    names = {'NTERM_X': 'xterm', 'NRES_X': 'xres', 'NTERM_Y': 'yterm', 'NRES_Y': 'yres'}
+    with open('%s/index.dat' % reread) as f:
+        for line in f:
+            t = line.split()
+            if line.strip().startswith('#') or len(t) < 2:
+                continue
+            key, val = t[0].upper(), t[1]
+            if key == 'ASYMM' and val == 'yes':
+                asymm = 1
+            elif key == 'NTERM':
+                nterm = int(val)
+            elif key == 'NRES':
+                nres = int(val)
+            elif key in names:
+                keys[names[key]] = int(val)
+            elif key == 'TRUNC':
+                trunc = float(val)
+    if asymm:
+        missing = [k for k in names if names[k] not in keys]
+        if missing:
+            print("Key not found in index.dat: %s !" % missing[0])
+            print("Try again, giving all of the following keys: %s" % " ".join(names))
+            sys.exit()
+    elif nres is None:
+        print("You need to give at least NRES in the index.dat file.")
+    return asymm, nterm, nres, trunc, keys
+
+
+def read_matrix(inputf, xterm, xres, yterm, yres, asymm, trunc):
+    """One matrices/NNNNN.dat -> sparse {(i, j): r} with r < trunc (conan.py:1051-1071)."""
+    frame = {}
+    for line in inputf:
+        t = line.split()
+        if line.strip().startswith('#') or not t:
+            continue
+        n1, n2, r = int(t[0]), int(t[1]), float(t[2])
+        if xterm <= n1 < xterm + xres and r < trunc and (asymm or n1 < n2):
+            frame[(n1, n2)] = r
+    return frame
+
+
+def _levels_from_reread(reread, layout, trunc, asymm):
+    """All matrices of a REREAD folder as a level stack.  The distances in those files are multiples of
+    the level width of the run that wrote them; the width is recovered from the data."""
+    files = []
+    for i in range(100000):
+        name = "%s/%05i.dat" % (reread, i)
+        if os.path.exists(name):
+            files.append(name)
+    if not files:
+        print("Reread folder is empty, will quit now.")
+        sys.exit()
+    print("Found %i matrices to reread from." % len(files))
+    lay = layout
+    dense = np.full((len(files), lay.xres, lay.yres), trunc, dtype=np.float64)
+    for n, name in enumerate(files):
+        a = np.loadtxt(name, ndmin=2)
+        if a.size == 0:
+            continue
+        i, j, r = a[:, 0].astype(int) - lay.xterm, a[:, 1].astype(int) - lay.yterm, a[:, 2]
+        ok = (i >= 0) & (i < lay.xres) & (j >= 0) & (j < lay.yres) & (r < trunc)
+        if not asymm:
+            ok &= i < j
+        dense[n, i[ok], j[ok]] = r[ok]
+    vals = np.unique(np.round(dense, 6))
+    gaps = np.diff(vals)
+    gaps = gaps[gaps > 1e-6]
+    dx = gaps.min() if len(gaps) else trunc
+    nlev = int(round(trunc / dx)) + 1
+    for cand in (nlev, 2 * (nlev - 1) + 1, 4 * (nlev - 1) + 1):     # the smallest gap may be several levels wide
+        dxc = trunc / (cand - 1)
+        if cand <= lv.MAX_NLEVELS and np.abs(vals / dxc - np.rint(vals / dxc)).max() * dxc <= 0.51e-4:
+            nlev, dx = cand, dxc
+            break
+    else:
+        print("The REREAD matrices are not multiples of one level width with at most %d levels." % lv.MAX_NLEVELS)
+        sys.exit()
+    k = np.rint(dense / dx).astype(np.uint16)
+    if asymm:
+        stack = k.reshape(len(files), -1)
+    else:
+        iu = np.triu_indices(lay.xres, 1)
+        stack = np.ascontiguousarray(k[:, iu[0], iu[1]])
+    return stack, nlev
+
+
+# ------------------------------------------------------------------------------------------------
 # stage 2
 # ------------------------------------------------------------------------------------------------
 class Stage2Result:
@@ -473,9 +565,6 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
     global _last_stage2
     import torch
     from . import stage1, stage2
-    if reread:
-        print("REREAD is not wired to the GPU path yet; run from the trajectory or from dmf.xpm.")
-        sys.exit()
     if dimer:
         print("Dimer mode is not available in this implementation; continuing without it.")
     dev = torch.device(device)
@@ -488,7 +577,14 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
         layout = tables.Layout(nres=nres, nterm=nterm)
         xres = yres = nres
         xterm = yterm = nterm
-    if s1 is not None and s1.geom.nres == nres and s1.nlevels == nlevels:
+    if reread:
+        stack_host, nlevels = _levels_from_reread(reread, layout, trunc, asymm)
+        d_stack = None
+        begin = begin if begin else 0            # conan.py:751-754: REREAD times are begin + n * dt
+        dt = dt if dt else 1000
+        times_all = begin + dt * np.arange(stack_host.shape[0], dtype=np.float64)
+        end = None
+    elif s1 is not None and s1.geom.nres == nres and s1.nlevels == nlevels:
         times_all = s1.times
         if asymm:
             xs, ys = sorted(xdict), sorted(ydict)      # xpm residue numbers (1-based) of the X and Y selections
@@ -604,7 +700,7 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
 
     density_r2_metric = {}
     if pearson_inter:
-        density_r2_metric = _pearson_inter(host_levels(), values, layout, trunc, asymm)
+        density_r2_metric = _pearson_inter(d_stack, nlevels, layout, asymm)
 
     print("number of frames=", len(time_vec))
     avg_d, life_d = tab.metric_dicts()
@@ -617,19 +713,25 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
     return (begin, dt, time_vec, pairs_list, pairs_legend, vectors, avg_d, life_d, density_r2_metric) + tab.interact_dicts()
 
 
-def _pearson_inter(levels_host, values, layout, trunc, asymm):
-    """Inter-residue correlation of weighted contact numbers (conan.py:669-695, :843-850, :876-887)."""
-    w = (trunc - values[levels_host]) / trunc                  # [nf, P]
-    nf = w.shape[0]
+def _pearson_inter(d_stack, nlevels, layout, asymm):
+    """Inter-residue correlation of weighted contact numbers (conan.py:669-695, :843-850, :876-887).
+
+    The per-frame, per-residue sums come from conan_residue_weights (exact integers in level units;
+    the common factor 1/(nlevels-1) does not change a correlation); the nres x nres correlation of
+    those short vectors is a library call on the device."""
+    import torch
+    from . import stage3
+    w = stage3.residue_weights(d_stack, nlevels, not asymm, layout.xres, layout.yres if asymm else 0)   # [nf, n] int32
     out = {}
 
-    def corr_table(vecs, path, term):
-        n = vecs.shape[0]
-        varying = np.array([len(set(v)) > 1 for v in vecs])
-        with np.errstate(invalid="ignore", divide="ignore"):
-            c = np.corrcoef(vecs) if n > 1 else np.ones((1, 1))
-        c = np.where(np.outer(varying, varying), c, 0.0)
-        np.fill_diagonal(c, np.where(varying, 1.0, 0.0))
+    def corr_table(vecs, path, term):          # vecs: [nf, n] on the device
+        n = vecs.shape[1]
+        v = vecs.double()
+        varying = (v.max(dim=0).values != v.min(dim=0).values)
+        c = torch.corrcoef(v.T) if n > 1 else torch.ones((1, 1), dtype=torch.float64, device=v.device)
+        c = torch.where(varying[:, None] & varying[None, :], c, torch.zeros_like(c))
+        c = c.cpu().numpy().copy()
+        np.fill_diagonal(c, np.where(varying.cpu().numpy(), 1.0, 0.0))
         with open(path, "w") as f:
             for i in range(n):
                 f.write("".join("%5i %5i %15.6f\n" % (term + i, term + j, c[i, j]) for j in range(n)))
@@ -637,16 +739,11 @@ def _pearson_inter(levels_host, values, layout, trunc, asymm):
         return c
 
     if asymm:
-        m = w.reshape(nf, layout.xres, layout.yres)
-        corr_table(m.sum(axis=2).T, "aggregate/pearson_map_density.x.dat", layout.xterm)
-        corr_table(m.sum(axis=1).T, "aggregate/pearson_map_density.y.dat", layout.yterm)
+        corr_table(w[:, :layout.xres], "aggregate/pearson_map_density.x.dat", layout.xterm)
+        corr_table(w[:, layout.xres:], "aggregate/pearson_map_density.y.dat", layout.yterm)
         return out
+    c = corr_table(w, "aggregate/pearson_map_density.dat", layout.xterm)
     n = layout.nres
-    iu = np.triu_indices(n, 1)
-    res_vec = np.zeros((n, nf))
-    np.add.at(res_vec, iu[0], w.T)
-    np.add.at(res_vec, iu[1], w.T)
-    c = corr_table(res_vec, "aggregate/pearson_map_density.dat", layout.xterm)
     for i in range(n):
         for j in range(n):
             if i != j:
@@ -678,7 +775,16 @@ def main(argv=None):
     if g.get('run_mdmat', False) and not g['reread']:
         mdmat_run('', g['traj'], g['coord'], g['nlevels'], trunc, g['mean'], g['begin'], g['end'], g['dt'], g['indexf'],
                   pbc=g.get('pbc', True), group=g.get('group'), write_xpm=g.get('write_xpm'))
-    if _last_stage1 is not None:
+    if g['reread']:
+        asymm, nterm_r, nres, trunc, keys = read_index_folder(g['reread'])
+        g['nterm'] = nterm_r
+        nlevels = nchar = dict_legend = inputf = None
+        if asymm:
+            print("asymm, xterm, xres, yterm, yres, trunc", asymm, keys['xterm'], keys['xres'], keys['yterm'], keys['yres'], trunc)
+            asymm_data = (1, 1, keys['xres'], keys['yres'], keys['xterm'], keys['yterm'])
+        else:
+            print("asymm, nterm, nres, trunc", asymm, nterm_r, nres, trunc)
+    elif _last_stage1 is not None:
         nres, nlevels, nchar = _last_stage1.geom.nres, _last_stage1.nlevels, (1 if _last_stage1.nlevels <= 88 else 2)
         dict_legend, trunc = None, _last_stage1.trunc
         inputf = None

@@ -54,6 +54,18 @@ def level_range(d_stack, P, frame_mask=None):
     return kmin.cpu().numpy().astype(np.int64), kmax.cpu().numpy().astype(np.int64)
 
 
+def residue_weights(d_stack, nlevels, symmetric, xres, yres=0):
+    """int32 device tensor [nf, nres] (or [nf, xres + yres]): weighted contact numbers in level units."""
+    lib = _lib.load()
+    dev = d_stack.device
+    nf, stride = d_stack.shape
+    n = xres if symmetric else xres + yres
+    out = torch.empty((nf, n), dtype=torch.int32, device=dev)
+    _lib.check(lib.conan_residue_weights(d_stack.data_ptr(), stride, nf, 1 if symmetric else 0, xres, yres, nlevels,
+                                         out.data_ptr(), _stream(dev)))
+    return out
+
+
 def linregress_all(d_stack, P, nlevels, d_lut, xs, shift, frame_mask=None):
     """scipy.stats.linregress(x_k, series_p) for every pair p and every row x_k of xs [K, nf].
 

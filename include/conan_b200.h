@@ -231,6 +231,12 @@ int conan_pearson_sums(const uint16_t* d_levels, int64_t levels_stride, int64_t 
 int conan_level_range(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
                       const uint8_t* d_frame_mask, uint32_t* d_kmin, uint32_t* d_kmax, void* stream);
 
+/* Weighted number of contacts of every residue in every frame, the residue_column of conan.py:843-850
+ * (weight_contacts :19-21), in level units: d_out [nf][n] int32 with n = nres (symmetric) or xres + yres,
+ * out[f][r] = sum over the pairs of residue r of (nlevels-1 - level).  Feeds PEARSON_INTER (:669-695). */
+int conan_residue_weights(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int32_t symmetric,
+                          int32_t xres, int32_t yres, int32_t nlevels, int32_t* d_out, void* stream);
+
 /* Builds a GEMM operand from the stack, centred and split into TF32 hi / lo parts (x = hi + lo).
  * rows_are_frames = 0: rows = the nsel selected pairs d_sel (indices into the P columns), K = frames,
  *     x = y - d_mean[row]                       -- the operand of np.cov(vectors), conan.py:1983.

@@ -166,3 +166,31 @@ def test_stage3_files_of_the_live_reference_case(lib, tmp_path):
         assert np.abs(got - want).max() <= tol, (key, np.abs(got - want).max())
         checked += 1
     assert checked >= 20
+
+
+def test_reread_matches_reference_goldens(lib, goldens, tmp_path):
+    """The reference's test 7: matrices of an earlier run are read back, differential maps are written."""
+    from conan_b200 import levels as lv
+    os.makedirs(str(tmp_path / "to_read"))
+    values = lv.legend_values(1.0, 1001)
+    for f in range(11):          # the reference's to_read/ folder is its own test-1 output
+        with open(str(tmp_path / "to_read" / ("%05d.dat" % f)), "w") as out:
+            out.write("# i  j   r_ij\n")
+            m = values[goldens["levels_sym"][f]]
+            for i in range(28):
+                out.write("".join("%4d %4d %9.4f\n" % (i + 1, j + 1, m[i, j]) for j in range(28)) + "\n")
+    with open(str(tmp_path / "to_read" / "index.dat"), "w") as out:
+        out.write("NTERM 1\nNRES 28\nDT 100000\nTRUNC 1.0\n")
+    _run_cli(str(tmp_path), "REREAD to_read/\nDR_MODE both\n")
+    lv_sym = goldens["levels_sym"].astype(np.int64)
+    for f in (0, 3, 10):
+        m = np.loadtxt(str(tmp_path / "matrices" / ("%05d.dat" % f)))
+        assert np.array_equal(np.rint(m[:, 2] * 1000).astype(int).reshape(28, 28), lv_sym[f])
+    for f in (1, 7):
+        di = np.loadtxt(str(tmp_path / "matrices" / ("%05d_dr.init.dat" % f)))
+        dp = np.loadtxt(str(tmp_path / "matrices" / ("%05d_dr.prev.dat" % f)))
+        assert np.array_equal(np.rint(di[:, 2] * 1000).astype(int).reshape(28, 28), lv_sym[f] - lv_sym[0])
+        assert np.array_equal(np.rint(dp[:, 2] * 1000).astype(int).reshape(28, 28), lv_sym[f] - lv_sym[f - 1])
+    tl = np.loadtxt(str(tmp_path / "aggregate" / "timeline.dat"))
+    want = goldens["1_ReadWrite/aggregate/timeline.dat"]
+    assert np.array_equal(tl[:, [0, 1, 4, 6]], want[:, [0, 1, 4, 6]])        # lifetimes and encounters as in test 1
