@@ -360,7 +360,10 @@ def run_ours(args):
             "roofline": {
                 "kernel": "mdmat_tile_kernel", "bound": "fp32", "achieved": tile_tflops, "peak": fp32_peak.value,
                 "unit": "TFLOP/s", "frac": tile_tflops / fp32_peak.value if fp32_peak.value else None,
-                "traffic": None, "ms": ms_tile,
+                # dram__bytes_read + dram__bytes_write of this kernel per pair-frame, from the committed ncu
+                # capture (profiles/r1_ncu_full_summary.txt: 0.336 GB + 0.944 GB per 1000 frames x 499 500 pairs)
+                "traffic": 2.564 * P * nf if (nres, ATOMS_PER_RES) == (1000, 8) else None, "traffic_unit": "bytes per launch",
+                "ms": ms_tile,
                 "peak_source": "FP32 FMA rate measured in this run (conan_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
                 "algorithmic": "8 flop x %.4g atom pairs (%.1f%% of residue pairs survive pruning)"
                                % (cnt[2], 100.0 * cnt[1] / (float(P) * nf)),
@@ -369,7 +372,9 @@ def run_ours(args):
             },
             "roofline_stats": {"kernel": "pair_stats_kernel (+combine)", "bound": "hbm", "achieved": stats_gbs,
                                "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": stats_gbs / pk["hbm_gbs"],
-                               "traffic": None, "ms": ms_stats, "peak_kind": pk_kind},
+                               # 1.0155 GB read + 0.126 GB written per 1000 frames x 499 500 pairs (same capture)
+                               "traffic": 2.286 * P * nf if nres == 1000 else None, "traffic_unit": "bytes per launch",
+                               "ms": ms_stats, "peak_kind": pk_kind},
             "stage_ms": {"prep_slots_kernel": ms_prep, "mdmat_tile_kernel": ms_tile, "pair_stats": ms_stats},
             "boundary_results": int(cnt[0]),
         }
