@@ -291,6 +291,43 @@ def cluster_trajectory(ctx, ks, trunc, trunc_inter, asymm):
     return D
 
 
+def zoom_on_pairs(ctx, zoom_list, trunc, inter_low, inter_high):
+    """zoom/dist_i_j.dat and zoom/2d_correlate_i_j.dat for every listed pair (conan.py:170-215, :1850-1859):
+    the pair's distance trace with its hysteresis state, and its Pearson correlation with every other pair."""
+    import torch
+    os.makedirs("zoom", exist_ok=True)
+    lay = ctx.layout
+    pi, pj = lay.pair_labels()
+    index = {(int(a), int(b)): n for n, (a, b) in enumerate(zip(pi, pj))}
+    listed = np.zeros(ctx.P, bool)
+    listed[ctx.seen] = True
+    varying = ctx.varying()
+    for pair in zoom_list:
+        p = index.get(pair, index.get(pair[::-1]))
+        if p is None or not listed[p]:
+            print("Warning, pair (%i, %i) in zoom list never formed an interaction!" % pair)
+            rvec = np.full(ctx.nf, trunc)
+        else:
+            col = ctx.d_stack[:, p].view(torch.int16).cpu().numpy().view(np.uint16)
+            rvec = ctx.lut_host[col].astype(np.float64)
+        inter = 0
+        # the reference compares float16 distances with the cut-offs, which numpy rounds to float16 first
+        lo16, hi16 = float(np.float16(inter_low)), float(np.float16(inter_high))
+        with open("zoom/dist_%i_%i.dat" % pair, "w") as f:
+            f.write("# t (ps) r (nm) interact?\n")
+            for t, r in zip(ctx.time_vec, rvec):
+                if r < lo16:
+                    inter = 1
+                elif r > hi16:
+                    inter = 0
+                f.write("%9d %12.6f %3i\n" % (t, r, inter))
+        r_all = np.zeros(ctx.P)
+        if len(set(rvec)) > 1:
+            res = stage3.linregress_all(ctx.d_stack, ctx.P, ctx.nlevels, ctx.lut, rvec[None], ctx.shift)
+            r_all = np.where(listed & varying, res["r"][0], 0.0)
+        ctx.write_map("zoom/2d_correlate_%i_%i.dat" % pair, ctx.to_map(r_all, 0.0), fmt="%5i %5i %12.6f\n")
+
+
 def run_all(opts, ret, s2, trunc, trunc_inter, nres, nterm, asymm_data):
     ctx = None
 
@@ -300,6 +337,9 @@ def run_all(opts, ret, s2, trunc, trunc_inter, nres, nterm, asymm_data):
             ctx = _Ctx(s2)
         return ctx
 
+    if opts.get('zoom'):
+        print("Zooming in on interesting residue pairs...")
+        zoom_on_pairs(context(), opts['zoom_list'], trunc, trunc_inter, opts.get('_trunc_inter_high', trunc_inter))
     if opts.get('pearson_time'):
         pearson_time(context())
         print("")
@@ -312,6 +352,6 @@ def run_all(opts, ret, s2, trunc, trunc_inter, nres, nterm, asymm_data):
         print("Starting contact map-based cluster analysis...")
         print("")
         cluster_trajectory(context(), opts['ks_traj'], trunc, trunc_inter, bool(asymm_data))
-    for k in ('pca_dir', 'blocking', 'k_res_clusters', 'zoom'):
+    for k in ('pca_dir', 'blocking', 'k_res_clusters'):
         if opts.get(k):
             print("The %s analysis is outside the accelerated path and not available in this build." % k.upper())

@@ -37,6 +37,7 @@ constexpr int kThreads = 192;
 constexpr int kTmemCols = 256;                       // two 128-column accumulators, used alternately
 constexpr int kChunkKb = 4;                          // k-blocks accumulated inside the tensor core before a drain
 constexpr int kUmmaK = 8;                           // TF32: 32 bytes per MMA along K
+constexpr int kBand = 8;                            // tile rows per band of the launch order
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -125,14 +126,15 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__
     __shared__ uint32_t tmem_base_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int tm = blockIdx.y, tn = blockIdx.x;
-    if (prm.symmetric) {
-        // blockIdx.x enumerates the upper triangle of tiles row by row
-        const int nt = (prm.N + kBN - 1) / kBN;
-        int t = blockIdx.x, r = 0;
-        while (t >= nt - r) { t -= nt - r; r++; }
-        tm = r; tn = r + t;
-    }
+    // Tiles are walked in bands of kBand tile rows, column by column inside a band, so the CTAs that
+    // are resident together share a few A row strips and B column strips in L2.
+    const int ntm = (prm.M + kBM - 1) / kBM, ntn = (prm.N + kBN - 1) / kBN;
+    const int band = (int)blockIdx.x / (kBand * ntn);
+    const int rows_in_band = min(kBand, ntm - band * kBand);
+    const int within = (int)blockIdx.x - band * kBand * ntn;
+    const int tn = within / rows_in_band;
+    const int tm = band * kBand + within % rows_in_band;
+    if (prm.symmetric && tn < tm) return;        // lower triangle: written by the mirror store of (tn, tm)
     const int m0 = tm * kBM, n0 = tn * kBN;
     const int nkb = prm.K / kBK;
     const int nchunks = (nkb + kChunkKb - 1) / kChunkKb;
@@ -323,7 +325,7 @@ extern "C" int conan_gemm_3xtf32(const float* d_a_hi, const float* d_a_lo, int32
     const size_t smem = (size_t)kStages * kStageBytes + 1024;
     CONAN_CUDA_TRY(cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tmn = (M + kBM - 1) / kBM, tnn = (N + kBN - 1) / kBN;
-    dim3 grid = symmetric ? dim3((unsigned)(tnn * (tnn + 1) / 2), 1) : dim3((unsigned)tnn, (unsigned)tmn);
+    dim3 grid((unsigned)(tmn * tnn), 1);
     gemm3x_kernel<<<grid, kThreads, smem, stream>>>(mAh, mAl, mBh, mBl, prm);
     CONAN_CUDA_TRY(cudaGetLastError());
     return CONAN_OK;

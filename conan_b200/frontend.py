@@ -814,5 +814,6 @@ def main(argv=None):
     if inputf is not None:
         inputf.close()
     from . import analyses
+    g['_trunc_inter_high'] = trunc_inter_high
     analyses.run_all(g, ret, _last_stage2, trunc, trunc_inter, nres, nterm, asymm_data)
     return ret

@@ -97,7 +97,7 @@ def synthetic_levels(seed, nf, nres, nlevels, lo, hi):
     return full
 
 
-def run_case(name, full, times, trunc, nlevels, keywords, obs=None):
+def run_case(name, full, times, trunc, nlevels, keywords, obs=None, extra_files=None):
     work = tempfile.mkdtemp(prefix="conan_golden_")
     with open(os.path.join(work, "dmf.xpm"), "w") as f:
         xpm.write_xpm(f, full, times, trunc, nlevels)
@@ -110,6 +110,9 @@ def run_case(name, full, times, trunc, nlevels, keywords, obs=None):
             for t, row in zip(times, obs):
                 f.write("%d %s\n" % (t, " ".join("%.6f" % v for v in row)))
         text += "PEARSON_OBS obs.dat\n"
+    for fname, content in (extra_files or {}).items():
+        with open(os.path.join(work, fname), "w") as f:
+            f.write(content)
     g = ref_runner.run_reference(work, text)
     out = {"in/levels_full": full, "in/times": np.asarray(times, np.float64), "in/trunc": np.float64(trunc),
            "in/nlevels": np.int64(nlevels), "in/keywords": np.array(text)}
@@ -132,21 +135,29 @@ def run_case(name, full, times, trunc, nlevels, keywords, obs=None):
 def main():
     if not ref_runner.available():
         sys.exit("needs /root/reference")
-    peptide_fixture()
-    reference_goldens()
+    only = sys.argv[1] if len(sys.argv) > 1 else None
+    if not only:
+        peptide_fixture()
+        reference_goldens()
     nf, nres, nl = 48, 12, 101
     times = np.arange(nf) * 100
     full = synthetic_levels(11, nf, nres, nl, 0.5, 0.6)
     rng = np.random.default_rng(5)
     obs = np.stack([np.linspace(0, 1, nf) + rng.normal(0, 0.2, nf), rng.normal(0, 1, nf)], axis=1)
-    run_case("hyst", full, times, 1.0, nl,
-             "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nPEARSON_TIME yes\nPEARSON_INTER yes\nPCA_MAKE 3\n"
-             "K_TRAJ_CLUSTERS 2-3\nDR_MODE both\n", obs)
-    run_case("equalcut", full, times, 1.0, nl, "TRUNC_INTER 0.45\nMATRICES no\nPEARSON_TIME yes\n")
-    run_case("default", full[:20], times[:20], 1.0, nl, "MATRICES no\n")
-    run_case("asym", full, times, 1.0, nl,
-             "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nSTART_X 1\nNRES_X 5\nNTERM_X 1\nSTART_Y 6\nNRES_Y 7\nNTERM_Y 6\n"
-             "MATRICES no\nPEARSON_TIME yes\nK_TRAJ_CLUSTERS 2\n")
+    if not only:
+        run_case("hyst", full, times, 1.0, nl,
+                 "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nPEARSON_TIME yes\nPEARSON_INTER yes\nPCA_MAKE 3\n"
+                 "K_TRAJ_CLUSTERS 2-3\nDR_MODE both\n", obs)
+        run_case("equalcut", full, times, 1.0, nl, "TRUNC_INTER 0.45\nMATRICES no\nPEARSON_TIME yes\n")
+        run_case("default", full[:20], times[:20], 1.0, nl, "MATRICES no\n")
+        run_case("asym", full, times, 1.0, nl,
+                 "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nSTART_X 1\nNRES_X 5\nNTERM_X 1\nSTART_Y 6\nNRES_Y 7\nNTERM_Y 6\n"
+                 "MATRICES no\nPEARSON_TIME yes\nK_TRAJ_CLUSTERS 2\n")
+    if only in (None, "zoom"):
+        run_case("zoom", full[:30], times[:30], 1.0, nl, "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nMATRICES no\nZOOM_LIST zoom.txt\n",
+                 extra_files={"zoom.txt": "# pairs\n2 7\n9 3\n1 12\n"})
+        if only:
+            return
     # finer legend: 1001 levels, trunc 1.5 (dx = 0.0015, not a multiple of 1e-4)
     full2 = synthetic_levels(12, 30, 9, 1001, 0.5, 0.6)
     run_case("fine", full2, np.arange(30) * 500 + 1000, 1.5, 1001,

@@ -194,3 +194,35 @@ def test_reread_matches_reference_goldens(lib, goldens, tmp_path):
     tl = np.loadtxt(str(tmp_path / "aggregate" / "timeline.dat"))
     want = goldens["1_ReadWrite/aggregate/timeline.dat"]
     assert np.array_equal(tl[:, [0, 1, 4, 6]], want[:, [0, 1, 4, 6]])        # lifetimes and encounters as in test 1
+
+
+def test_zoom_matches_live_reference(lib, tmp_path):
+    """ZOOM_LIST: distance trace with hysteresis state and the pair's correlation with every other pair."""
+    from conan_b200 import xpm
+    c = np.load(os.path.join(GOLDEN, "case_zoom.npz"))
+    with open(str(tmp_path / "dmf.xpm"), "w") as f:
+        xpm.write_xpm(f, c["in/levels_full"], c["in/times"], float(c["in/trunc"]), int(c["in/nlevels"]))
+    with open(str(tmp_path / "zoom.txt"), "w") as f:
+        f.write("# pairs\n2 7\n9 3\n1 12\n")
+    _run_cli(str(tmp_path), str(c["in/keywords"]))
+    n = 0
+    for key in c.files:
+        if key.startswith("file/zoom/"):
+            got = np.loadtxt(str(tmp_path / key[len("file/"):]))
+            # scipy's pearsonr keeps the float16 dtype of `vectors`, so the reference's own numbers carry
+            # float16 rounding (~5e-4); the distance traces are exact
+            tol = 3.0e-3 if "2d_correlate" in key else 2.0e-6
+            assert got.shape == c[key].shape and np.abs(got - c[key]).max() <= tol, key
+            n += 1
+    assert n == 6
+    # ... and against float64 Pearson coefficients of the reference's own `vectors`, to print precision
+    vec = c["ret/vectors"].astype(np.float64)
+    pairs = [tuple(int(v) for v in row) for row in c["ret/pairs_list"]]
+    zp = [q for q in ((2, 7), (3, 9), (1, 12)) if q in pairs][0]
+    zi = pairs.index(zp)
+    got = np.loadtxt(str(tmp_path / "zoom" / ("2d_correlate_%d_%d.dat" % zp)))
+    table = {(int(a), int(b)): v for a, b, v in got}
+    for row, pair in enumerate(pairs):
+        want = np.corrcoef(vec[zi], vec[row])[0, 1] if vec[row].std() > 0 else 0.0
+        assert abs(table[pair] - want) < 2e-6 and abs(table[pair[::-1]] - want) < 2e-6, pair
+
