@@ -301,8 +301,11 @@ def choose_group(groups, stdin=None, preset=None):
 
 
 def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf, pbc=True, group=None,
-              write_xpm=None, device="cuda"):
-    """Stage 1 in-process: the work of `gmx mdmat -frames` (conan.py:1437-1453).  `program` is ignored."""
+              write_xpm=None, device="cuda", block=None):
+    """Stage 1 in-process: the work of `gmx mdmat -frames` (conan.py:1437-1453).  `program` is ignored.
+
+    block = (x0, xres, y0, yres), 0-based residues of the index group: compute only that X x Y block
+    (an asymmetric run does not need the other pairs; no dmf.xpm is written then)."""
     global _last_stage1
     import torch
     from . import stage1
@@ -334,7 +337,11 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     if use_pbc and triclinic:
         print("Triclinic boxes are not supported by the minimum-image code; distances are computed without PBC.")
         use_pbc = False
-    geom = stage1.Geometry(res_start)
+    nres_all = len(res_start) - 1
+    if block is not None and (block[0] < 0 or block[2] < 0 or block[0] + block[1] > nres_all or block[2] + block[3] > nres_all):
+        print("The X / Y residue ranges do not fit the %d residues of the index group; computing all pairs." % nres_all)
+        block = None
+    geom = stage1.Geometry(res_start, *block) if block is not None else stage1.Geometry(res_start)
     dev = torch.device(device)
     levels = torch.zeros((len(frames), geom.stride), dtype=torch.uint16, device=dev)
     counters = torch.zeros(3, dtype=torch.int64, device=dev)
@@ -355,7 +362,9 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     entries = float(len(frames)) * geom.nres * geom.nres
     if write_xpm is None:
         write_xpm = entries <= XPM_WRITE_LIMIT
-    if write_xpm:
+    if block is not None:
+        print("Asymmetric run: only the %d x %d block of residue pairs was computed; dmf.xpm is not written." % (geom.xres, geom.yres))
+    elif write_xpm:
         with open("dmf.xpm", "w") as f:
             xpm.write_xpm(f, _last_stage1.square_host(), _last_stage1.times, trunc, nlevels)
     else:
@@ -586,7 +595,9 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
         end = None
     elif s1 is not None and s1.geom.nres == nres and s1.nlevels == nlevels:
         times_all = s1.times
-        if asymm:
+        if asymm and not s1.geom.symmetric:
+            stack_host, d_stack = None, s1.levels      # stage 1 already computed exactly this block
+        elif asymm:
             xs, ys = sorted(xdict), sorted(ydict)      # xpm residue numbers (1-based) of the X and Y selections
             sq = s1.square_host()
             full = np.full((len(times_all), xres, yres), nlevels - 1, np.uint16)
@@ -772,9 +783,18 @@ def main(argv=None):
     trunc = g['trunc']
     trunc_input = trunc
     handle_backups()
+    block = None
+    if g['asymm'] and 'xdict' in g and 'ydict' in g and not g.get('write_xpm'):
+        xs, ys = sorted(g['xdict']), sorted(g['ydict'])
+        straight = (xs == list(range(xs[0], xs[0] + len(xs))) and ys == list(range(ys[0], ys[0] + len(ys)))
+                    and [g['xdict'][m] - g['xterm'] for m in xs] == list(range(len(xs)))
+                    and [g['ydict'][m] - g['yterm'] for m in ys] == list(range(len(ys)))
+                    and len(xs) == g['xres'] and len(ys) == g['yres'])
+        if straight:
+            block = (xs[0] - 1, len(xs), ys[0] - 1, len(ys))
     if g.get('run_mdmat', False) and not g['reread']:
         mdmat_run('', g['traj'], g['coord'], g['nlevels'], trunc, g['mean'], g['begin'], g['end'], g['dt'], g['indexf'],
-                  pbc=g.get('pbc', True), group=g.get('group'), write_xpm=g.get('write_xpm'))
+                  pbc=g.get('pbc', True), group=g.get('group'), write_xpm=g.get('write_xpm'), block=block)
     if g['reread']:
         asymm, nterm_r, nres, trunc, keys = read_index_folder(g['reread'])
         g['nterm'] = nterm_r

@@ -226,3 +226,16 @@ def test_zoom_matches_live_reference(lib, tmp_path):
         want = np.corrcoef(vec[zi], vec[row])[0, 1] if vec[row].std() > 0 else 0.0
         assert abs(table[pair] - want) < 2e-6 and abs(table[pair[::-1]] - want) < 2e-6, pair
 
+
+
+def test_asymmetric_from_trajectory_computes_only_the_block(lib, goldens, tmp_path):
+    """START_X / START_Y with a trajectory: stage 1 runs in block mode and the reference's test-8 goldens still match."""
+    out = _run_cli(str(tmp_path), "TRAJ %s/sample.xtc\nCOORD %s/peptide.gro\nTRUNC 1.0\nNLEVEL 1001\nNRES_X 14\nNRES_Y 14\n"
+                   "NTERM_X 1\nNTERM_Y 15\nSTART_X 1\nSTART_Y 15\n" % (GOLDEN, GOLDEN))
+    assert "only the 14 x 14 block" in out and not (tmp_path / "dmf.xpm").exists()
+    for name in ("timeline", "mdmat_average_rmsf", "native_contacts", "time_mdmat_rmsd", "total_interactions.x",
+                 "total_interactions.y"):
+        got = np.loadtxt(str(tmp_path / "aggregate" / (name + ".dat")))
+        assert _close(got, goldens["8_Asymmetric/aggregate/%s.dat" % name]), name
+    m = np.loadtxt(str(tmp_path / "matrices" / "00007.dat"))
+    assert np.array_equal(np.rint(m[:, 2] * 1000).astype(int).reshape(14, 14), goldens["levels_asym"][7])
