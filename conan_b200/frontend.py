@@ -637,7 +637,7 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
     P, stride = layout.P, lv.padded_stride(layout.P)
     if d_stack is not None:
         if len(keep) != d_stack.shape[0]:
-            d_stack = d_stack[torch.from_numpy(keep).to(dev)].contiguous()
+            d_stack = d_stack.view(torch.int16)[torch.from_numpy(keep).to(dev)].contiguous().view(torch.uint16)
     else:
         buf = np.zeros((len(keep), stride), np.uint16)
         buf[:, :P] = stack_host[keep]

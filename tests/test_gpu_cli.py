@@ -239,3 +239,21 @@ def test_asymmetric_from_trajectory_computes_only_the_block(lib, goldens, tmp_pa
         assert _close(got, goldens["8_Asymmetric/aggregate/%s.dat" % name]), name
     m = np.loadtxt(str(tmp_path / "matrices" / "00007.dat"))
     assert np.array_equal(np.rint(m[:, 2] * 1000).astype(int).reshape(14, 14), goldens["levels_asym"][7])
+
+
+def test_begin_end_dt_select_frames(lib, orc, goldens, tmp_path):
+    """BEGIN / END / DT: gmx's -b/-e/-dt filter and CONAN's own (time-begin) % dt test pick the same frames."""
+    from conan_b200 import levels as lv
+    _run_cli(str(tmp_path), "TRAJ %s/sample.xtc\nCOORD %s/peptide.gro\nTRUNC 1.0\nNLEVEL 1001\nBEGIN 200000\nEND 900000\n"
+             "DT 200000\nTRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\n" % (GOLDEN, GOLDEN))
+    frames = [2, 4, 6, 8]
+    assert sorted(os.listdir(str(tmp_path / "matrices"))) == ["%05d.dat" % n for n in range(4)]
+    for n, f in enumerate(frames):
+        m = np.loadtxt(str(tmp_path / "matrices" / ("%05d.dat" % n)))
+        assert np.array_equal(np.rint(m[:, 2] * 1000).astype(int).reshape(28, 28), goldens["levels_sym"][f])
+    values = lv.legend_values(1.0, 1001)
+    lo, hi, eq = lv.level_thresholds(values, 0.5, 0.6)
+    want = orc.pair_stats(orc.condensed(goldens["levels_sym"][frames]), lo, hi, eq)
+    nc = np.loadtxt(str(tmp_path / "aggregate" / "native_contacts.dat"))
+    assert np.array_equal(nc[:, 0], np.array([200.0, 400.0, 600.0, 800.0]))
+    assert np.array_equal(nc[:, 1], want["native"]) and np.array_equal(nc[:, 2], want["nonnative"])
