@@ -181,6 +181,12 @@ __device__ __forceinline__ float dist2_exact(float dx, float dy, float dz) {
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
 }
 
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+    float d;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));   // FMNMX3
+    return d;
+}
+
 // Minimum over one chunk of ICH i-atom slots against all cj atoms of residue j, expanded form.
 // aI: i-role planes (-2x', -2y', -2z', |a'|^2) of residue i; aJ: j-role planes (x', y', z') of j;
 // (Dx, Dy, Dz) = centre_j - centre_i.  Returns min over the chunk of |a - b|^2 (approximately).
@@ -195,12 +201,19 @@ __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, co
         az[u] = aI[2 * pstride + (a0 + u) * kTile];
         mu[u] = 3.0e38f;
     }
-#pragma unroll 2
-    for (int b = 0; b < cj; b++) {
+    // two j atoms per trip, combined with the three-input minimum; slots past cj repeat atom 0 of
+    // the residue (prep_slots_kernel) and kpad is a multiple of 4, so the odd trip reads valid data
+#pragma unroll 1
+    for (int b = 0; b < cj; b += 2) {
         const float bx = aJ[b * kTile] + Dx, by = aJ[pstride + b * kTile] + Dy, bz = aJ[2 * pstride + b * kTile] + Dz;
+        const float cx = aJ[(b + 1) * kTile] + Dx, cy = aJ[pstride + (b + 1) * kTile] + Dy,
+                    cz = aJ[2 * pstride + (b + 1) * kTile] + Dz;
         const float nb = fmaf(bz, bz, fmaf(by, by, bx * bx));
+        const float nc = fmaf(cz, cz, fmaf(cy, cy, cx * cx));
 #pragma unroll
-        for (int u = 0; u < ICH; u++) mu[u] = fminf(mu[u], fmaf(az[u], bz, fmaf(ay[u], by, fmaf(ax[u], bx, nb))));
+        for (int u = 0; u < ICH; u++)
+            mu[u] = fmin3(mu[u], fmaf(az[u], bz, fmaf(ay[u], by, fmaf(ax[u], bx, nb))),
+                          fmaf(az[u], cz, fmaf(ay[u], cy, fmaf(ax[u], cx, nc))));
     }
 #pragma unroll
     for (int u = 0; u < ICH; u++) m = fminf(m, mu[u] + aI[3 * pstride + (a0 + u) * kTile]);
@@ -241,8 +254,12 @@ __device__ __forceinline__ int exact_pair_warp(const MdmatParams& prm, int64_t f
     const int b0 = prm.res_start[gj], nb = prm.res_start[gj + 1] - b0;
     const float* x = prm.xyz + (size_t)f * prm.natoms * 3;
     float m = prm.trunc2;
+    const float rnb = __frcp_rn((float)nb);
     for (int idx = lane; idx < na * nb; idx += 32) {
-        const int a = a0 + idx / nb, b = b0 + idx % nb;
+        // idx / nb without the integer division: exact for idx < 2^14 (na, nb <= 128), because
+        // (idx + 0.5) / nb stays 0.5 / nb away from an integer and the float error is below that
+        const int q = (int)(((float)idx + 0.5f) * rnb);
+        const int a = a0 + q, b = b0 + idx - q * nb;
         float dx = x[3 * a] - x[3 * b], dy = x[3 * a + 1] - x[3 * b + 1], dz = x[3 * a + 2] - x[3 * b + 2];
         if (prm.pbc) { dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz); }
         m = fminf(m, dist2_exact(dx, dy, dz));
@@ -315,6 +332,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     uint16_t* slow = list + kListCap;                                     // [kSlowCap]
     uint64_t* bar = reinterpret_cast<uint64_t*>(slow + kSlowCap);
     int* counters = reinterpret_cast<int*>(bar + 1);   // [0] list [1] redo list [2] near [3] evals [4] survivors
+    int* rowbase = counters + 6;                        // [64] element index of pair (gi0 + i, gj0) in a frame row
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t blk = blockIdx.x;
@@ -394,6 +412,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         }
         (isI ? grpI : grpJ)[l] = make_float4(s0.x, s0.y, s0.z, R);
         (isI ? cntI : cntJ)[l] = prm.cnt[gr];
+        if (isI) rowbase[l] = pair_idx(gr, gj0);
     }
 
     // ---- fill: every pair of the tile starts at the "beyond trunc" level -------------------
@@ -402,22 +421,24 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         const int sub = lane >> 4, l16 = lane & 15;
         const uint32_t fillv = (uint32_t)maxlevel * 0x00010001u;
         const int jlo0 = max(0, j_beg - gj0), jhi = min(kTile, j_end - gj0);
-        for (int rg = warp * 2 + sub; rg < nfb * kTile; rg += 2 * kWarps) {
-            const int g = rg >> 6, i = rg & 63;
+        const uint16_t ml = (uint16_t)maxlevel;
+        for (int i = warp * 2 + sub; i < kTile; i += 2 * kWarps) {
             const int gi = gi0 + i;
             if (gi < i_beg || gi >= i_end) continue;
             const int jlo = diag ? max(jlo0, i + 1) : jlo0;
-            if (jlo >= jhi) continue;
-            uint16_t* row = prm.levels + (size_t)(f0 + g) * prm.stride + pair_idx(gi, gj0);
-            // 8-byte aligned body, scalar head and tail
-            const int mis = (int)((reinterpret_cast<uintptr_t>(row + jlo) >> 1) & 3);   // elements past alignment
-            const int head = min((4 - mis) & 3, jhi - jlo);
-            const int body0 = jlo + head;
-            const int nq = (jhi - body0) >> 2;
-            if (l16 < head) row[jlo + l16] = (uint16_t)maxlevel;
-            if (l16 < nq) *reinterpret_cast<uint2*>(row + body0 + 4 * l16) = make_uint2(fillv, fillv);
-            const int tail0 = body0 + 4 * nq;
-            if (l16 < jhi - tail0) row[tail0 + l16] = (uint16_t)maxlevel;
+            const int n = jhi - jlo;
+            if (n <= 0) continue;
+            uint16_t* p = prm.levels + (size_t)f0 * prm.stride + pair_idx(gi, gj0) + jlo;
+            for (int g = 0; g < nfb; g++, p += prm.stride) {
+                // 8-byte aligned body, scalar head and tail
+                const int mis = (int)((reinterpret_cast<uintptr_t>(p) >> 1) & 3);   // elements past alignment
+                const int head = min((4 - mis) & 3, n);
+                const int nq = (n - head) >> 2;
+                if (l16 < head) p[l16] = ml;
+                if (l16 < nq) *reinterpret_cast<uint2*>(p + head + 4 * l16) = make_uint2(fillv, fillv);
+                const int tail0 = head + 4 * nq;
+                if (l16 < n - tail0) p[tail0 + l16] = ml;
+            }
         }
     }
     __syncthreads();   // spheres, counts and the fill are in place
@@ -463,7 +484,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 level = exact_pair(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, near);
             }
             if (level < maxlevel)
-                prm.levels[(size_t)(f0 + g) * prm.stride + pair_idx(gi0 + i, gj0 + j)] = (uint16_t)level;
+                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + j] = (uint16_t)level;
         }
         __syncthreads();
         const int nslow = min(counters[1], kSlowCap);
@@ -477,7 +498,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             }
             const int level = exact_pair_warp(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, lane, near);
             if (lane == 0)
-                prm.levels[(size_t)(f0 + g) * prm.stride + pair_idx(gi0 + i, gj0 + j)] = (uint16_t)level;
+                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + j] = (uint16_t)level;
         }
         near = __reduce_add_sync(0xffffffffu, near);
         evals = __reduce_add_sync(0xffffffffu, evals);
@@ -582,7 +603,7 @@ size_t mdmat_smem_bytes(int kpad, int fb) {
     s += (size_t)(fb + 1) * 2 * kTile * sizeof(float4);         // per-frame and per-group spheres
     s += 2 * kTile * sizeof(int);                               // counts
     s += (size_t)(kListCap + kSlowCap) * sizeof(uint16_t);      // survivor and redo lists
-    s += 8 + 6 * sizeof(int);                                   // mbarrier + counters
+    s += 8 + 6 * sizeof(int) + kTile * sizeof(int);             // mbarrier + counters + row bases
     return (s + 15) & ~(size_t)15;
 }
 
