@@ -187,19 +187,39 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) {
     return d;
 }
 
+// Packed FP32 pairs (FFMA2): one issue slot for two fused multiply-adds.  ptxas turns a pair built
+// from the same scalar twice into the broadcast operand form, so only the i side lives in pairs.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 // Minimum over one chunk of ICH i-atom slots against all cj atoms of residue j, expanded form.
 // aI: i-role planes (-2x', -2y', -2z', |a'|^2) of residue i; aJ: j-role planes (x', y', z') of j;
 // (Dx, Dy, Dz) = centre_j - centre_i.  Returns min over the chunk of |a - b|^2 (approximately).
+// Each product-sum is a chain of three fused multiply-adds rounded exactly as the scalar form.
 template <int ICH>
 __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, const float* __restrict__ aJ,
                                                 int pstride, int a0, int cj, float Dx, float Dy, float Dz, float m) {
-    float ax[ICH], ay[ICH], az[ICH], mu[ICH];
+    f32x2 ax[ICH / 2], ay[ICH / 2], az[ICH / 2];
+    float mu[ICH];
 #pragma unroll
-    for (int u = 0; u < ICH; u++) {
-        ax[u] = aI[(a0 + u) * kTile];
-        ay[u] = aI[pstride + (a0 + u) * kTile];
-        az[u] = aI[2 * pstride + (a0 + u) * kTile];
-        mu[u] = 3.0e38f;
+    for (int u = 0; u < ICH / 2; u++) {
+        ax[u] = pack2(aI[(a0 + 2 * u) * kTile], aI[(a0 + 2 * u + 1) * kTile]);
+        ay[u] = pack2(aI[pstride + (a0 + 2 * u) * kTile], aI[pstride + (a0 + 2 * u + 1) * kTile]);
+        az[u] = pack2(aI[2 * pstride + (a0 + 2 * u) * kTile], aI[2 * pstride + (a0 + 2 * u + 1) * kTile]);
+        mu[2 * u] = 3.0e38f;
+        mu[2 * u + 1] = 3.0e38f;
     }
     // two j atoms per trip, combined with the three-input minimum; slots past cj repeat atom 0 of
     // the residue (prep_slots_kernel) and kpad is a multiple of 4, so the odd trip reads valid data
@@ -210,10 +230,18 @@ __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, co
                     cz = aJ[2 * pstride + (b + 1) * kTile] + Dz;
         const float nb = fmaf(bz, bz, fmaf(by, by, bx * bx));
         const float nc = fmaf(cz, cz, fmaf(cy, cy, cx * cx));
+        const f32x2 BX = pack2(bx, bx), BY = pack2(by, by), BZ = pack2(bz, bz), NB = pack2(nb, nb);
+        const f32x2 CX = pack2(cx, cx), CY = pack2(cy, cy), CZ = pack2(cz, cz), NC = pack2(nc, nc);
 #pragma unroll
-        for (int u = 0; u < ICH; u++)
-            mu[u] = fmin3(mu[u], fmaf(az[u], bz, fmaf(ay[u], by, fmaf(ax[u], bx, nb))),
-                          fmaf(az[u], cz, fmaf(ay[u], cy, fmaf(ax[u], cx, nc))));
+        for (int u = 0; u < ICH / 2; u++) {
+            const f32x2 vb = fma2(az[u], BZ, fma2(ay[u], BY, fma2(ax[u], BX, NB)));
+            const f32x2 vc = fma2(az[u], CZ, fma2(ay[u], CY, fma2(ax[u], CX, NC)));
+            float b0, b1, c0, c1;
+            unpack2(vb, b0, b1);
+            unpack2(vc, c0, c1);
+            mu[2 * u] = fmin3(mu[2 * u], b0, c0);
+            mu[2 * u + 1] = fmin3(mu[2 * u + 1], b1, c1);
+        }
     }
 #pragma unroll
     for (int u = 0; u < ICH; u++) m = fminf(m, mu[u] + aI[3 * pstride + (a0 + u) * kTile]);
