@@ -46,6 +46,10 @@ SIGNATURES = {
                                         c_void_p, c_i32, c_void_p, c_i32]),
     "conan_xtc_encode": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32,
                                         c_f32, c_void_p, c_size, ctypes.POINTER(c_size)]),
+    "conan_write_matrices": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32, c_i32, c_i32,
+                                            c_void_p, c_i32, c_i32, c_void_p, c_void_p, ctypes.c_char_p, c_i32]),
+    "conan_write_xpm": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i32, c_i32, c_i32, c_void_p, ctypes.c_char_p,
+                                       ctypes.c_char_p, ctypes.c_char_p, c_i32, c_i32, ctypes.c_char_p, c_i32, c_i32]),
     "conan_mdmat_workspace_bytes": (c_size, [c_i64, c_i32, c_i32, c_i32]),
     "conan_mdmat_frames": (ctypes.c_int, [c_void_p, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_i32,
                                           c_i32, c_i32, c_i32, c_i32, c_f32, c_i32, c_i32, c_void_p,

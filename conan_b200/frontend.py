@@ -16,7 +16,7 @@ import sys
 import numpy as np
 
 from . import levels as lv
-from . import tables, topology, xpm
+from . import _lib, tables, topology, xpm
 from ._lib import ConanError
 
 # ------------------------------------------------------------------------------------------------
@@ -365,8 +365,9 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     if block is not None:
         print("Asymmetric run: only the %d x %d block of residue pairs was computed; dmf.xpm is not written." % (geom.xres, geom.yres))
     elif write_xpm:
-        with open("dmf.xpm", "w") as f:
-            xpm.write_xpm(f, _last_stage1.square_host(), _last_stage1.times, trunc, nlevels)
+        import torch
+        flat = levels.view(torch.int16).cpu().numpy().view(np.uint16)
+        xpm.write_xpm_stack("dmf.xpm", flat, True, geom.nres, geom.nres, _last_stage1.times, trunc, nlevels)
     else:
         print("dmf.xpm not written (%.3g entries); the level stack stays on the GPU." % entries)
     return _last_stage1
@@ -535,33 +536,15 @@ def write_matrix(outputf, time, xterm, xres, yterm, yres, trunc, dict_frame, dr,
         outputf.write("\n")
 
 
-def _write_matrix_files(levels_host, values, layout, trunc, dr_mode, nframes):
-    """matrices/%05d.dat (+ _dr.init / _dr.prev) straight from the level stack."""
+def _write_matrix_files(levels_host, values, layout, trunc, dr_mode, nframes, symmetric):
+    """matrices/%05d.dat (+ _dr.init / _dr.prev) straight from the level stack (conan_write_matrices)."""
     lay = layout
-    prefix = [["%4d %4d " % (i + lay.xterm, j + lay.yterm) for j in range(lay.yres)] for i in range(lay.xres)]
-    head = "# i  j   r_ij\n# r_ij is the shortest distance between any atom of residues  i, j.\n"
-    head_dr = ("# i  j   dr_ij\n# dr_ij is the change (compared to the previous frame)\n"
-               "# in shortest distance between any atom of residues  i, j.\n")
-
-    def dump(path, mat, header):
-        with open(path, "w") as f:
-            f.write(header)
-            for i in range(lay.xres):
-                f.write("".join(prefix[i][j] + "%9.4f\n" % mat[i, j] for j in range(lay.yres)))
-                f.write("\n")
-
-    first = prev = None
-    for n in range(nframes):
-        mat = lay.to_matrix(values[levels_host[n]], diag=0.0)
-        dump("matrices/%05d.dat" % n, mat, head)
-        if first is not None:
-            if dr_mode in (1, 3):
-                dump("matrices/%05d_dr.init.dat" % n, mat - first, head_dr)
-            if dr_mode in (2, 3):
-                dump("matrices/%05d_dr.prev.dat" % n, mat - prev, head_dr)
-        else:
-            first = mat
-        prev = mat
+    stack = np.ascontiguousarray(levels_host[:nframes], dtype=np.uint16)
+    vals = np.ascontiguousarray(values, dtype=np.float64)
+    lib = _lib.load()
+    _lib.check(lib.conan_write_matrices(stack.ctypes.data, stack.shape[1], stack.shape[0], 0, 1 if symmetric else 0,
+                                        lay.xterm, lay.xres, lay.yterm, lay.yres, vals.ctypes.data, len(vals),
+                                        int(dr_mode), None, None, b"matrices", min(32, os.cpu_count() or 1)))
 
 
 def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, trunc, trunc_inter, trunc_inter_high,
@@ -662,7 +645,7 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
         return levels_host
 
     if matrices:
-        _write_matrix_files(host_levels(), values, layout, trunc, dr_mode, nf)
+        _write_matrix_files(host_levels(), values, layout, trunc, dr_mode, nf, not asymm)
     if nf == 1:
         print("Detected a single frame. Not very dynamic, but we will plot the distances and finish.")
         sys.exit()

@@ -39,6 +39,7 @@ extern "C" {
 #define CONAN_ERR_CUDA (-2)   /* a CUDA runtime / driver call failed */
 #define CONAN_ERR_FORMAT (-3) /* malformed trajectory data */
 #define CONAN_ERR_SIZE (-4)   /* problem exceeds a documented limit / workspace too small */
+#define CONAN_ERR_IO (-5)     /* a file could not be opened or written */
 
 /* Library version (major*10000 + minor*100 + patch). */
 int conan_version(void);
@@ -258,6 +259,37 @@ int conan_gemm_3xtf32(const float* d_a_hi, const float* d_a_lo, int32_t M, const
                       const float* d_b_lo, int32_t N, int64_t K, int64_t ld, int32_t epilogue, float alpha,
                       const double* d_row_norm2, const double* d_col_norm2, int32_t symmetric, float* d_c,
                       int64_t ldc, void* stream);
+
+/* ------------------------------------------------------------------------------------ */
+/* Text writers of the file contract (host).  HOST pointers.         */
+/* ------------------------------------------------------------------------------------ */
+
+/* matrices/NNNNN.dat exactly as write_matrix prints them (conan.py:570-597: two comment lines, then
+ * "%4d %4d %9.4f" per residue pair, a blank line after each x residue), straight from the level
+ * stack, frames spread over nthreads host threads.
+ * h_levels    [nf][levels_stride] uint16, pair order as conan_mdmat_frames writes it (symmetric:
+ *             condensed i<j, the diagonal prints 0; else the xres x yres block, x-major).
+ * file_index0 number of the first file (frame f goes to <directory>/<file_index0+f, %05d>.dat).
+ * values      [nlevels] legend values (float64); values[level] is the printed distance.
+ * dr_mode     bit 0: also NNNNN_dr.init.dat (change since frame 0), bit 1: NNNNN_dr.prev.dat (change
+ *             since the previous frame), conan.py:829-838; frame 0 of the run gets neither.
+ * h_first_row / h_prev_row: rows of the run's frame 0 and of the frame before this batch, needed
+ *             only when dr_mode != 0 and file_index0 > 0. */
+int conan_write_matrices(const uint16_t* h_levels, int64_t levels_stride, int64_t nf, int64_t file_index0,
+                         int32_t symmetric, int32_t xterm, int32_t xres, int32_t yterm, int32_t yres,
+                         const double* values, int32_t nlevels, int32_t dr_mode, const uint16_t* h_first_row,
+                         const uint16_t* h_prev_row, const char* directory, int32_t nthreads);
+
+/* The multi-frame dmf.xpm `gmx mdmat -frames` leaves behind and read_index / read_next_time /
+ * read_frame parse (conan.py:455-567): per frame the comment header with `title: "t=<ps> ps"`, the
+ * legend block, the axis comments and yres rows (last y residue first) of xres codes.
+ * legend_block, axes_block: the text between the header and the rows (identical in every frame).
+ * codes       [nlevels][nchar] characters, nchar = 1 or 2.
+ * append != 0 adds the frames to an existing file (batches of one run). */
+int conan_write_xpm(const uint16_t* h_levels, int64_t levels_stride, int64_t nf, int32_t symmetric, int32_t xres,
+                    int32_t yres, const double* times, const char* legend_block, const char* axes_block,
+                    const char* codes, int32_t nchar, int32_t nlevels, const char* path, int32_t append,
+                    int32_t nthreads);
 
 /* ------------------------------------------------------------------------------------ */
 /* Measurement helpers (bench.py only).                                                  */
