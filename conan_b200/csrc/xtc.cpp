@@ -10,6 +10,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <thread>
 #include <vector>
 
@@ -351,6 +352,7 @@ extern "C" int conan_xtc_encode(const float* xyz, const float* boxes, const int3
                 }
             uint32_t sizeint[3];
             int bitsint[3] = {0, 0, 0}, bitsize;
+            int smallidx, first_smallidx;
             for (int d = 0; d < 3; d++) sizeint[d] = (uint32_t)(mx[d] - mn[d] + 1);
             if ((sizeint[0] | sizeint[1] | sizeint[2]) > 0xffffff) {
                 for (int d = 0; d < 3; d++) bitsint[d] = bits_for(sizeint[d]);
@@ -359,23 +361,96 @@ extern "C" int conan_xtc_encode(const float* xyz, const float* boxes, const int3
                 bitsize = bits_for_product(sizeint);
             }
             BitWriter bw{bits};
-            for (int a = 0; a < natoms; a++) {
+            auto send3 = [&](int nb, const uint32_t sz[3], const uint32_t c[3]) {
+                unsigned __int128 v = ((unsigned __int128)c[0] * sz[1] + c[1]) * sz[2] + c[2];
+                int left = nb;
+                while (left > 8) { bw.put((uint32_t)(v & 0xff), 8); v >>= 8; left -= 8; }
+                if (left > 0) bw.put((uint32_t)(v & ((1u << left) - 1)), left);
+            };
+            // the xdr3dfcoord scheme: an atom in full, then a run of up to eight atoms as small
+            // differences to their predecessor while they stay close (water molecules, side chains);
+            // the width of the small codes adapts to how close successive atoms are
+            int64_t mindiff = INT64_MAX;
+            for (int a = 1; a < natoms; a++) {
+                int64_t dsum = 0;
+                for (int d = 0; d < 3; d++) dsum += std::llabs((int64_t)ints[3 * (size_t)a + d] - ints[3 * (size_t)(a - 1) + d]);
+                mindiff = std::min(mindiff, dsum);
+            }
+            const int kLastIdx = kNumMagic - 1;
+            smallidx = kFirstIdx;
+            while (smallidx < kLastIdx && kMagicInts[smallidx] < mindiff) smallidx++;
+            first_smallidx = smallidx;
+            const int maxidx = std::min(kLastIdx, smallidx + 8), minidx = maxidx - 8;
+            int smaller = kMagicInts[std::max(kFirstIdx, smallidx - 1)] / 2;
+            int smallnum = kMagicInts[smallidx] / 2;
+            const int larger = kMagicInts[maxidx] / 2;
+            uint32_t sizesmall[3] = {(uint32_t)kMagicInts[smallidx], (uint32_t)kMagicInts[smallidx], (uint32_t)kMagicInts[smallidx]};
+            auto within = [&](const int32_t* p, const int32_t* q, int lim) {
+                for (int d = 0; d < 3; d++)
+                    if (std::llabs((int64_t)p[d] - q[d]) >= lim) return false;
+                return true;
+            };
+            int i = 0, prevrun = -1;
+            int32_t prevcoord[3] = {0, 0, 0};
+            uint32_t tmp[8 * 3];
+            while (i < natoms) {
+                int32_t* cur = &ints[3 * (size_t)i];
+                int is_small = 0, is_smaller;
+                if (smallidx < maxidx && i >= 1 && within(cur, prevcoord, larger)) is_smaller = 1;
+                else if (smallidx > minidx) is_smaller = -1;
+                else is_smaller = 0;
+                if (i + 1 < natoms && within(cur, cur + 3, smallnum)) {
+                    for (int d = 0; d < 3; d++) std::swap(cur[d], cur[3 + d]);   // the pair is stored swapped
+                    is_small = 1;
+                }
                 uint32_t c[3];
-                for (int d = 0; d < 3; d++) c[d] = (uint32_t)(ints[3 * (size_t)a + d] - mn[d]);
+                for (int d = 0; d < 3; d++) c[d] = (uint32_t)(cur[d] - mn[d]);
                 if (bitsize == 0) {
                     for (int d = 0; d < 3; d++) bw.put(c[d], bitsint[d]);
                 } else {
-                    unsigned __int128 v = ((unsigned __int128)c[0] * sizeint[1] + c[1]) * sizeint[2] + c[2];
-                    int left = bitsize;
-                    while (left > 8) { bw.put((uint32_t)(v & 0xff), 8); v >>= 8; left -= 8; }
-                    if (left > 0) bw.put((uint32_t)(v & ((1u << left) - 1)), left);
+                    send3(bitsize, sizeint, c);
                 }
-                bw.put(0, 1);  // no run of small deltas follows
+                for (int d = 0; d < 3; d++) prevcoord[d] = cur[d];
+                i++;
+                cur += 3;
+                int run = 0;
+                if (is_small == 0 && is_smaller == -1) is_smaller = 0;
+                while (is_small && run < 8 * 3) {
+                    if (is_smaller == -1) {
+                        int64_t d2 = 0;
+                        for (int d = 0; d < 3; d++) { const int64_t dd = (int64_t)cur[d] - prevcoord[d]; d2 += dd * dd; }
+                        if (d2 >= (int64_t)smaller * smaller) is_smaller = 0;
+                    }
+                    for (int d = 0; d < 3; d++) tmp[run++] = (uint32_t)(cur[d] - prevcoord[d] + smallnum);
+                    for (int d = 0; d < 3; d++) prevcoord[d] = cur[d];
+                    i++;
+                    cur += 3;
+                    is_small = (i < natoms && within(cur, prevcoord, smallnum)) ? 1 : 0;
+                }
+                if (run != prevrun || is_smaller != 0) {
+                    prevrun = run;
+                    bw.put(1, 1);
+                    bw.put((uint32_t)(run + is_smaller + 1), 5);
+                } else {
+                    bw.put(0, 1);
+                }
+                for (int k = 0; k < run; k += 3) send3(smallidx, sizesmall, tmp + k);
+                if (is_smaller != 0) {
+                    smallidx += is_smaller;
+                    if (is_smaller < 0) {
+                        smallnum = smaller;
+                        smaller = kMagicInts[std::max(kFirstIdx, smallidx - 1)] / 2;
+                    } else {
+                        smaller = smallnum;
+                        smallnum = kMagicInts[smallidx] / 2;
+                    }
+                    sizesmall[0] = sizesmall[1] = sizesmall[2] = (uint32_t)kMagicInts[smallidx];
+                }
             }
             bw.flush();
             putf(head + 56, precision);
             for (int d = 0; d < 3; d++) { put32(head + 60 + 4 * d, (uint32_t)mn[d]); put32(head + 72 + 4 * d, (uint32_t)mx[d]); }
-            put32(head + 84, kFirstIdx);
+            put32(head + 84, (uint32_t)first_smallidx);
             put32(head + 88, (uint32_t)bits.size());
             size_t padded = (bits.size() + 3) & ~(size_t)3;
             fsz = 92 + padded;

@@ -69,6 +69,50 @@ class XtcFile:
                                             out.ctypes.data, nthreads))
         return out
 
+    def decode_device(self, frame_ids=None, atom_sel=None, device="cuda", out=None, stream=None):
+        """Decode frames on the GPU (conan_xtc_decode_device): the compressed bytes of the frame range are
+        copied to the device and each frame is decoded by one thread.  Returns a float32 device tensor
+        [n, nsel, 3]; raises ConanError if any frame is malformed (this call synchronises to check)."""
+        import torch
+        lib = _lib.load()
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise _lib.ConanError(-1, "decode_device needs a CUDA device")
+        if frame_ids is None:
+            frame_ids = np.arange(self.nframes, dtype=np.int64)
+        frame_ids = np.ascontiguousarray(frame_ids, dtype=np.int64)
+        if frame_ids.size and (frame_ids.min() < 0 or frame_ids.max() >= self.nframes):
+            raise _lib.ConanError(-1, "frame index out of range")
+        nout = self.natoms if atom_sel is None else len(atom_sel)
+        if out is None:
+            out = torch.empty((frame_ids.size, nout, 3), dtype=torch.float32, device=dev)
+        assert out.is_cuda and out.dtype == torch.float32 and out.is_contiguous() and out.numel() == frame_ids.size * nout * 3
+        if frame_ids.size == 0:
+            return out
+        # the byte range that holds the requested frames (frames are 4-byte multiples, so it stays aligned)
+        lo, last = int(frame_ids.min()), int(frame_ids.max())
+        b0 = int(self.offsets[lo])
+        b1 = int(self.offsets[last + 1]) if last + 1 < self.nframes else int(self._buf.size)
+        d_data = torch.from_numpy(np.array(self._buf[b0:b1])).to(dev)      # (the mapping itself is read-only)
+        d_off = torch.from_numpy(self.offsets[frame_ids] - b0).to(dev)
+        d_slot = None
+        if atom_sel is not None:
+            slot = np.full(self.natoms, -1, np.int32)
+            slot[np.asarray(atom_sel, dtype=np.int64)] = np.arange(nout, dtype=np.int32)
+            d_slot = torch.from_numpy(slot).to(dev)
+        d_status = torch.full((frame_ids.size,), -1, dtype=torch.int32, device=dev)
+        st = stream if stream is not None else torch.cuda.current_stream(dev).cuda_stream
+        with torch.cuda.device(dev):
+            _lib.check(lib.conan_xtc_decode_device(d_data.data_ptr(), b1 - b0, d_off.data_ptr(), frame_ids.size,
+                                                   self.natoms, None if d_slot is None else d_slot.data_ptr(), nout,
+                                                   out.data_ptr(), d_status.data_ptr(), st))
+        bad = torch.nonzero(d_status).flatten()
+        if bad.numel():
+            k = int(bad[0].item())
+            raise _lib.ConanError(-3, "frame %d of the trajectory is malformed (decoder status %d)"
+                                  % (int(frame_ids[k]), int(d_status[k].item())))
+        return out
+
 
 def write_xtc(path, xyz, boxes=None, times=None, steps=None, precision=1000.0):
     """Write float32 [nf, natoms, 3] coordinates (nm) as an .xtc trajectory."""

@@ -67,11 +67,27 @@ int conan_xtc_decode(const uint8_t* data, size_t nbytes, const int64_t* offsets,
                      const int64_t* frame_ids, int64_t nsel_frames, int32_t natoms,
                      const int32_t* atom_sel, int32_t nsel, float* xyz_out, int32_t nthreads);
 
-/* Write frames as a valid (uncompressed-run) .xtc into `out` (capacity cap bytes); *nbytes gets
+/* Write frames as an .xtc (xdr3dfcoord compression with runs of small differences) into `out`
+ * (capacity cap bytes); *nbytes gets
  * the size needed/used.  Used to materialise synthetic trajectories as real trajectory files. */
 int conan_xtc_encode(const float* xyz, const float* boxes, const int32_t* steps,
                      const float* times, int64_t nframes, int32_t natoms, float precision,
                      uint8_t* out, size_t cap, size_t* nbytes);
+
+/* The same decode on the GPU: the compressed file bytes are copied to the device
+ * as they are and every frame is decoded by one thread (a frame's bit stream is one dependent
+ * chain).  Coordinates are bit-identical to conan_xtc_decode's.
+ * d_data     the file bytes (or a 4-byte aligned slice of them) on the device, nbytes long.
+ * d_offsets  [nframes] byte offset inside d_data of every frame to decode (conan_xtc_index gives
+ *            them for the whole file; subtract the slice start).
+ * d_slot     [natoms] output row of each atom, -1 = not in the index group; NULL = all atoms
+ *            (then nsel == natoms).  d_xyz [nframes][nsel][3] float32 nm.
+ * d_status   [nframes] int32 out: 0 = decoded, 1 = bad header, 2 = bad code-size index, 3 = run
+ *            past the last atom, 4 = bit stream longer than the frame.  The call only enqueues the
+ *            kernel; the caller checks d_status after synchronising. */
+int conan_xtc_decode_device(const uint8_t* d_data, int64_t nbytes, const int64_t* d_offsets, int64_t nframes,
+                            int32_t natoms, const int32_t* d_slot, int32_t nsel, float* d_xyz,
+                            int32_t* d_status, void* stream);
 
 /* ------------------------------------------------------------------------------------ */
 /* Stage 1: per-frame residue-residue minimum-distance matrix, quantised to xpm levels.  */

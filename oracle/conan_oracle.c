@@ -132,10 +132,11 @@ static void receiveints(bitreader *b, int n, int nbits, const unsigned int sizes
     for (i = n - 1; i > 0; i--) {
         num = 0;
         for (j = nbytes - 1; j >= 0; j--) {
-            num = (num << 8) | bytes[j];
-            p = num / (int)sizes[i];
+            /* unsigned as in xdrfile (sizes[] is unsigned there): sizes up to 2^24 make num << 8 reach 2^32 */
+            num = (int)(((unsigned int)num << 8) | (unsigned int)bytes[j]);
+            p = (int)((unsigned int)num / sizes[i]);
             bytes[j] = p;
-            num = num - p * (int)sizes[i];
+            num = (int)((unsigned int)num - (unsigned int)p * sizes[i]);
         }
         nums[i] = num;
     }

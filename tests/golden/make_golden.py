@@ -7,6 +7,7 @@ Nothing under tests/ reads /root/reference at test time; the GPU box has no refe
 Fixtures written
   sample.xtc            copy of the reference's 11-frame test trajectory (input data, 17 KB)
   peptide.gro           topology of its 399 atoms, extracted from test/md.tpr, frame-0 coordinates
+  ubi_12.xtc            first 12 frames of applications/1_ubi_unfold/pull_500ps.xtc (input data, 52 KB)
   ref_goldens.npz       the reference's own golden outputs (test/*/correct_output) parsed to arrays,
                         plus the 11 x 28 x 28 golden level matrices of test 1 and the 14 x 14 of test 8
   case_*.npz            inputs and outputs of the UNMODIFIED reference run here (oracle/ref_runner.py)
@@ -77,6 +78,13 @@ def peptide_fixture():
     box = x.boxes[0].diagonal()
     topology.write_gro(os.path.join(OUT, "peptide.gro"), top, xyz0, box, "ACE-(33..58)-NME peptide of the CONAN tests")
     print("peptide.gro:", top.natoms, "atoms")
+    # the first 12 frames of the reference's ubiquitin unfolding trajectory (1231 atoms, written by gmx):
+    # a second real compressed stream for the decoders
+    data = open(os.path.join(REF, "applications/1_ubi_unfold/pull_500ps.xtc"), "rb").read()
+    xu = XtcFile(data)
+    with open(os.path.join(OUT, "ubi_12.xtc"), "wb") as f:
+        f.write(data[:int(xu.offsets[12])])
+    print("ubi_12.xtc:", int(xu.offsets[12]), "bytes,", xu.natoms, "atoms")
 
 
 def synthetic_levels(seed, nf, nres, nlevels, lo, hi):

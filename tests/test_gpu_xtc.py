@@ -1,0 +1,82 @@
+"""conan_xtc_decode_device (one thread per frame on the GPU) against the host decoder and the oracle:
+bit-identical coordinates on the reference's own trajectories and on synthetic compressed ones."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    return torch
+
+
+@pytest.mark.parametrize("name", ["sample.xtc", "ubi_12.xtc"])
+def test_reference_trajectories(torch_cuda, name):
+    from conan_b200.xtc import XtcFile
+    from oracle import oracle
+    path = os.path.join(HERE, "golden", name)
+    x = XtcFile(path)
+    host = x.decode()
+    dev = x.decode_device().cpu().numpy()
+    assert np.array_equal(dev, host)
+    assert np.array_equal(dev, oracle.xtc_decode(open(path, "rb").read())[2])
+    # a frame subset in arbitrary order and an atom selection
+    ids = np.array([x.nframes - 1, 0, 3, 3, 7])
+    sel = np.arange(5, x.natoms, 3, dtype=np.int32)
+    assert np.array_equal(x.decode_device(frame_ids=ids, atom_sel=sel).cpu().numpy(), host[ids][:, sel])
+
+
+def test_synthetic_compressed(torch_cuda, tmp_path):
+    from conan_b200 import synth
+    from conan_b200.xtc import XtcFile, write_xtc
+    xyz, _, L = synth.make_trajectory(300, 700, seed=4)
+    p = str(tmp_path / "c3.xtc")
+    write_xtc(p, xyz, boxes=np.tile(np.eye(3) * L, (700, 1, 1)), times=np.arange(700) * 100.0)
+    x = XtcFile(p)
+    host = x.decode()
+    assert np.abs(host - xyz).max() < 1.5e-6
+    assert np.array_equal(x.decode_device().cpu().numpy(), host)
+    sel = np.flatnonzero(np.arange(x.natoms) % 8 < 5).astype(np.int32)
+    ids = np.arange(3, 700, 7)
+    assert np.array_equal(x.decode_device(frame_ids=ids, atom_sel=sel).cpu().numpy(), host[ids][:, sel])
+
+
+def test_small_and_wide_systems(torch_cuda, tmp_path):
+    from conan_b200.xtc import XtcFile, write_xtc
+    rng = np.random.default_rng(1)
+    cases = [(3, 9.0, 1000.0), (9, 9.0, 1000.0), (10, 9.0, 1000.0), (257, 9.0, 1000.0),
+             (40, 200.0, 100000.0), (40, 100.0, 100000.0)]
+    for natoms, width, precision in cases:
+        xyz = np.round(rng.uniform(-2, width, size=(5, natoms, 3)) * 1000) / 1000
+        p = str(tmp_path / "t.xtc")
+        write_xtc(p, xyz, precision=precision)
+        x = XtcFile(p)
+        assert np.array_equal(x.decode_device().cpu().numpy(), x.decode()), (natoms, width)
+
+
+def test_malformed_frames_are_reported(torch_cuda, tmp_path):
+    from conan_b200 import _lib, synth
+    from conan_b200.xtc import XtcFile, write_xtc
+    xyz, _, L = synth.make_protein_like(30, 6, seed=2)
+    p = str(tmp_path / "m.xtc")
+    write_xtc(p, xyz)
+    data = bytearray(open(p, "rb").read())
+    x = XtcFile(bytes(data))
+    # break the code-size index of frame 2 (header field at +84): the index scan does not look at it
+    off = int(x.offsets[2])
+    data[off + 84:off + 88] = (200).to_bytes(4, "big")
+    bad = XtcFile(bytes(data))
+    with pytest.raises(_lib.ConanError) as e:
+        bad.decode_device()
+    assert "frame 2" in str(e.value)
+    # the other frames still decode
+    ids = np.array([0, 1, 3, 4, 5])
+    assert np.array_equal(bad.decode_device(frame_ids=ids).cpu().numpy(), x.decode(frame_ids=ids))

@@ -50,6 +50,32 @@ def test_encode_roundtrip_and_small_systems(lib, orc, tmp_path):
         assert np.array_equal(x.times, np.arange(5) * 2.0)
 
 
+def test_encode_uses_runs_on_clustered_atoms(lib, orc, tmp_path):
+    """Protein-like coordinates: neighbouring atoms are close, so the encoder emits runs of small
+    differences with an adapting code width; both decoders must read them back identically."""
+    from conan_b200 import synth
+    from conan_b200.xtc import XtcFile, write_xtc
+    for seed, nres in ((5, 57), (9, 200)):
+        xyz, _, L = synth.make_protein_like(nres, 7, seed=seed)
+        p = str(tmp_path / ("p%d.xtc" % nres))
+        nbytes = write_xtc(p, xyz, boxes=np.tile(np.eye(3) * L, (7, 1, 1)), times=np.arange(7) * 10.0)
+        assert nbytes < 0.5 * xyz.size * 4          # compressed well below 12 bytes per atom
+        x = XtcFile(p)
+        got = x.decode()
+        assert np.abs(got - xyz).max() < 1.5e-6
+        _, _, oxyz = orc.xtc_decode(open(p, "rb").read())
+        assert np.array_equal(got, oxyz)
+    # wide systems at high precision: sizes above 2^24 switch to per-component bit fields (200 nm), sizes
+    # between 2^23 and 2^24 give 70..72-bit packed triples and the widest small codes (100 nm)
+    for width in (200.0, 100.0):
+        xyz = np.round(np.random.default_rng(2).uniform(0, width, size=(2, 40, 3)) * 1000) / 1000
+        p = str(tmp_path / "wide.xtc")
+        write_xtc(p, xyz, precision=100000.0)
+        got = XtcFile(p).decode()
+        _, _, oxyz = orc.xtc_decode(open(p, "rb").read())
+        assert np.array_equal(got, oxyz) and np.abs(got - xyz).max() < 5e-5
+
+
 def test_truncated_file_is_an_error(lib, tmp_path):
     from conan_b200.xtc import XtcFile
     from conan_b200._lib import ConanError
