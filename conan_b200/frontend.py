@@ -347,14 +347,14 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     counters = torch.zeros(3, dtype=torch.int64, device=dev)
     batch = max(1, min(len(frames), 2048))
     work = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
-    pinned = torch.empty((batch, geom.natoms, 3), dtype=torch.float32).pin_memory()
+    d_coords = torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev)
     for b0 in range(0, len(frames), batch):
         ids = frames[b0:b0 + batch]
-        x.decode(frame_ids=ids, atom_sel=sel, out=pinned.numpy()[:len(ids)])
-        d_xyz = pinned[:len(ids)].to(dev, non_blocking=True)
+        # the compressed frames go to the GPU as they are and are decoded there (conan_xtc_decode_device)
+        d_xyz = x.decode_device(frame_ids=ids, atom_sel=sel, device=dev, out=d_coords[:len(ids)])
         d_box = torch.from_numpy(np.ascontiguousarray(boxes[b0:b0 + batch]).reshape(-1, 9)).to(dev) if use_pbc else None
         stage1.mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, use_pbc, levels[b0:b0 + len(ids)], work, counters)
-        torch.cuda.synchronize(dev)      # the pinned buffer is reused by the next batch
+        torch.cuda.synchronize(dev)      # the coordinate buffer is reused by the next batch
     nb = int(counters[0].item())
     print("Computed %d distance matrices of %d residues (%d results within 2 ulp of a level boundary)."
           % (len(frames), geom.nres, nb))

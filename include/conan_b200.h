@@ -75,8 +75,8 @@ int conan_xtc_encode(const float* xyz, const float* boxes, const int32_t* steps,
                      uint8_t* out, size_t cap, size_t* nbytes);
 
 /* The same decode on the GPU: the compressed file bytes are copied to the device
- * as they are and every frame is decoded by one thread (a frame's bit stream is one dependent
- * chain).  Coordinates are bit-identical to conan_xtc_decode's.
+ * as they are and every frame is decoded by one warp (the run flags are walked sequentially, the
+ * groups of atoms between them in parallel).  Coordinates are bit-identical to conan_xtc_decode's.
  * d_data     the file bytes (or a 4-byte aligned slice of them) on the device, nbytes long.
  * d_offsets  [nframes] byte offset inside d_data of every frame to decode (conan_xtc_index gives
  *            them for the whole file; subtract the slice start).
