@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stage3", action="store_true", help="skip the stage-3 (Pearson / covariance / frame-frame) leg")
     ap.add_argument("--stage3-frames", type=int, default=50000)
+    ap.add_argument("--no-xtc", action="store_true", help="skip the trajectory-feed leg (xtc decode on the GPU vs host threads)")
+    ap.add_argument("--xtc-frames", type=int, default=2500)
     return ap.parse_args()
 
 
@@ -385,6 +387,8 @@ def run_ours(args):
                 "value": float(P) * ncpu / t_cpu, "unit": UNIT, "cores": 1, "kind": "port",
                 "sample": "first %d frames of the same %d-residue shard (%.1f s of one host core; host has %d cores); "
                           "gmx mdmat itself: unavailable on this box" % (ncpu, nres, t_cpu, os.cpu_count() or 0)}
+        if not args.no_xtc:
+            line["xtc_feed"] = run_xtc_feed(args, dev, xyz)
         if not args.no_stage3:
             del d_xyz, levels, work1, work2
             torch.cuda.empty_cache()
@@ -392,6 +396,64 @@ def run_ours(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_xtc_feed(args, dev, xyz):
+    """The trajectory feed of stage 1: the shard's first frames written as a real .xtc, decoded by the GPU
+    kernel (compressed bytes copied from pinned host memory inside the timed region) and by the host decoder
+    on all cores for comparison."""
+    import tempfile
+    import torch
+    from conan_b200 import _lib
+    from conan_b200.xtc import XtcFile, write_xtc
+    lib = _lib.load()
+    n = max(1, min(args.xtc_frames, xyz.shape[0]))
+    path = os.path.join(tempfile.mkdtemp(prefix="conan_bench_"), "shard.xtc")
+    nbytes = write_xtc(path, xyz[:n], times=np.arange(n, dtype=np.float32) * 100.0)
+    x = XtcFile(path)
+    natoms = x.natoms
+    h_data = torch.from_numpy(np.array(x._buf)).pin_memory()
+    d_data = torch.empty_like(h_data, device=dev)
+    d_off = torch.from_numpy(x.offsets).to(dev)
+    d_out = torch.empty((n, natoms, 3), dtype=torch.float32, device=dev)
+    d_status = torch.zeros(n, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def decode():
+        _lib.check(lib.conan_xtc_decode_device(d_data.data_ptr(), d_data.numel(), d_off.data_ptr(), n, natoms, None, natoms,
+                                               d_out.data_ptr(), d_status.data_ptr(), stream.cuda_stream))
+
+    def timed(fn, reps=3):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn()
+        torch.cuda.synchronize(dev)
+        a.record(stream)
+        for _ in range(reps):
+            fn()
+        b.record(stream)
+        torch.cuda.synchronize(dev)
+        return a.elapsed_time(b) / reps
+
+    d_data.copy_(h_data)
+    ms_kernel = timed(decode)
+
+    def feed():
+        d_data.copy_(h_data, non_blocking=True)
+        decode()
+    ms_feed = timed(feed)
+    assert int(d_status.abs().sum().item()) == 0
+    threads = os.cpu_count() or 1
+    host = np.empty((n, natoms, 3), np.float32)
+    t0 = time.time()
+    x.decode(out=host, nthreads=threads)
+    t_host = time.time() - t0
+    same = bool(np.array_equal(d_out.cpu().numpy(), host))
+    os.remove(path)
+    return {"workload": "first %d frames of the shard as .xtc (%d atoms, %.2f bytes per atom)" % (n, natoms, nbytes / n / natoms),
+            "kernel": "xtc_decode_kernel", "decode_ms": ms_kernel, "atoms_per_s": n * natoms / (ms_kernel * 1e-3),
+            "h2d_plus_decode_ms": ms_feed, "compressed_bytes": int(nbytes), "float_bytes": int(n * natoms * 12),
+            "host_decode": {"ms": t_host * 1e3, "threads": threads, "atoms_per_s": n * natoms / t_host},
+            "bit_identical_to_host_decoder": same}
 
 
 def run_stage3(args, dev):
