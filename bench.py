@@ -507,7 +507,19 @@ def run_stage3(args, dev):
     hi_, lo_, _ = stage3.build_operand(levels, d_sel, NLEVELS, lut, d_mean, rows_are_frames=False)
     cov = torch.empty((len(seen), len(seen)), dtype=torch.float32, device=dev)
     ms_cov = timed(lambda: stage3.gemm_3xtf32(hi_, lo_, hi_, lo_, nf, alpha=1.0 / (nf - 1), symmetric=True, out=cov), reps=2)
-    del hi_, lo_, cov
+    del hi_, lo_
+    # top eigenpairs of that covariance (PCA_MAKE 3): restarted block Krylov vs the dense float64 factorisation
+    t0 = time.time()
+    w_top, _ = stage3.top_eigenpairs(cov, 3)
+    torch.cuda.synchronize(dev)
+    t_eig = time.time() - t0
+    t0 = time.time()
+    w_dense = torch.linalg.eigvalsh(cov.double()).flip(0)[:3]
+    torch.cuda.synchronize(dev)
+    t_dense = time.time() - t0
+    eig = {"k": 3, "ms": t_eig * 1e3, "dense_eigvalsh_float64_ms": t_dense * 1e3,
+           "max_rel_diff": float(((w_top - w_dense).abs() / w_dense[0]).max().item())}
+    del cov, w_dense
     # frame-frame distances on the first 20 000 frames (configs[4] has 20k frames)
     nff = min(nf, 20000)
     fh, fl, n2 = stage3.build_operand(levels[:nff], d_sel, NLEVELS, lut, d_mean, rows_are_frames=True, scale=1.0 / (nres / np.sqrt(2.0)))
@@ -528,6 +540,7 @@ def run_stage3(args, dev):
                        "peak": tf32_peak, "frac": mma_cov / ms_cov / 1e9 / tf32_peak,
                        "useful_tflops": 1.0 * len(seen) * len(seen) * nf / ms_cov / 1e9,
                        "peak_note": "half of the measured bf16 burst (%s)" % kind},
+        "pca_eigenpairs": eig,
         "frame_frame": {"ms": ms_ff, "rows": nff, "k": int(len(seen)), "bound": "tensor", "achieved": mma_ff / ms_ff / 1e9,
                         "unit": "TFLOP/s (TF32 MMA flops issued, 3 products)", "peak": tf32_peak,
                         "frac": mma_ff / ms_ff / 1e9 / tf32_peak, "useful_tflops": 1.0 * nff * nff * len(seen) / ms_ff / 1e9},

@@ -166,9 +166,8 @@ def pca(ctx, npc):
     print("Done.")
     sum_var = float(torch.diagonal(cov).double().sum().item())
     print("Diagonalizing....")
-    w, v = torch.linalg.eigh(cov.double())
-    w = w.flip(0)[:npc].cpu().numpy()
-    v = v.flip(1)[:, :npc].contiguous()
+    w, v = stage3.top_eigenpairs(cov, npc)
+    w = w.cpu().numpy()
     # projections on the float16 mean-free vectors, as project_pc builds them (:430-450, :1981)
     dev = ctx.d_stack.device
     d_sel = torch.from_numpy(sel.astype(np.int64)).to(dev)

@@ -151,3 +151,48 @@ def frame_distances(d_stack, sel, nlevels, d_lut, mean, norm):
     d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
     hi, lo, n2 = build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
     return gemm_3xtf32(hi, lo, hi, lo, len(sel), epilogue=1, row_norm2=n2, col_norm2=n2, symmetric=True)
+
+
+def top_eigenpairs(cov, k, tol=1.0e-11, block_extra=6, depth=8, max_cycles=40, dense_below=2048):
+    """The k largest eigenpairs of a symmetric positive semi-definite device matrix: eigsh(cov, k) of
+    conan.py:1985-1990 without factorising the whole matrix.
+
+    Restarted block Krylov iteration with Rayleigh-Ritz in float64: per cycle the block of Ritz vectors is
+    multiplied `depth` times by the matrix (each product re-orthonormalised), the Krylov basis is
+    orthonormalised, the matrix projected onto it and the small problem solved densely.  Stops when the
+    residuals |A v - w v| of the k wanted pairs are below tol * w_max.  Returns (w [k] descending, v [n, k]),
+    float64 on the device.  Small matrices are solved densely."""
+    n = cov.shape[0]
+    k = int(min(k, n))
+    if n <= dense_below or k + block_extra >= n // 4:
+        w, v = torch.linalg.eigh(cov.double())
+        return w.flip(0)[:k].contiguous(), v.flip(1)[:, :k].contiguous()
+    a = cov.double()
+    a = 0.5 * (a + a.T)
+    b = k + block_extra
+    gen = torch.Generator(device=cov.device)
+    gen.manual_seed(20240229)
+    x = torch.randn((n, b), dtype=torch.float64, device=cov.device, generator=gen)
+    x, _ = torch.linalg.qr(x)
+    theta = None
+    for _ in range(max_cycles):
+        blocks = [x]
+        w_blk = x
+        for _ in range(depth):
+            w_blk, _ = torch.linalg.qr(a @ w_blk)
+            blocks.append(w_blk)
+        q, _ = torch.linalg.qr(torch.cat(blocks, dim=1))
+        q, _ = torch.linalg.qr(q - q @ (q.T @ q - torch.eye(q.shape[1], dtype=q.dtype, device=q.device)))   # second pass
+        aq = a @ q
+        t = q.T @ aq
+        theta_all, s = torch.linalg.eigh(0.5 * (t + t.T))
+        s = s.flip(1)[:, :b]
+        theta = theta_all.flip(0)[:b]
+        x = q @ s
+        res = torch.linalg.vector_norm(aq @ s - x * theta[None, :], dim=0)
+        if float(res[:k].max().item()) <= tol * float(theta[0].abs().item()):
+            break
+        x, _ = torch.linalg.qr(x)
+    else:
+        raise _lib.ConanError(-4, "top_eigenpairs did not converge (residual %.3g)" % float(res[:k].max().item()))
+    return theta[:k].contiguous(), x[:, :k].contiguous()

@@ -126,3 +126,34 @@ def test_gemm_general_rectangular(lib):
     got = stage3.gemm_3xtf32(ah, al, bh, bl, K, alpha=0.5).cpu().numpy()
     want = 0.5 * a.astype(np.float32).astype(np.float64) @ b.astype(np.float32).astype(np.float64).T
     assert _frob(got, want) < 2e-6, _frob(got, want)
+
+
+def test_top_eigenpairs_matches_dense(lib):
+    """Restarted block Krylov solver against torch.linalg.eigh on a covariance-like matrix with a slowly
+    decaying spectrum and a near-degenerate pair."""
+    import torch
+    from conan_b200 import stage3
+    dev = torch.device("cuda")
+    torch.manual_seed(1)
+    n, F = 2600, 900
+    scales = torch.logspace(0, -1.5, 30, device=dev, dtype=torch.float64)
+    scales[3] = scales[2] * (1 - 1e-5)            # nearly equal eigenvalues
+    X = torch.randn(n, 30, device=dev, dtype=torch.float64) @ (torch.randn(30, F, device=dev, dtype=torch.float64) * scales[:, None])
+    X += 0.02 * torch.randn(n, F, device=dev, dtype=torch.float64)
+    X -= X.mean(1, keepdim=True)
+    A = (X @ X.T / (F - 1)).float()
+    k = 8
+    w, v = stage3.top_eigenpairs(A, k, dense_below=0)
+    wd, vd = torch.linalg.eigh(A.double())
+    wd, vd = wd.flip(0)[:k], vd.flip(1)[:, :k]
+    assert torch.allclose(w, wd, rtol=1e-10, atol=0)
+    # eigenvectors up to sign; the near-degenerate pair only as a subspace
+    for i in (0, 1, 4, 5, 6, 7):
+        d = min((v[:, i] - vd[:, i]).abs().max().item(), (v[:, i] + vd[:, i]).abs().max().item())
+        assert d < 1e-7, (i, d)
+    P1 = v[:, 2:4] @ v[:, 2:4].T
+    P2 = vd[:, 2:4] @ vd[:, 2:4].T
+    assert (P1 - P2).abs().max().item() < 1e-6
+    # orthonormal and small residual
+    assert (v.T @ v - torch.eye(k, device=dev, dtype=torch.float64)).abs().max().item() < 1e-12
+    assert torch.linalg.vector_norm(A.double() @ v - v * w[None], dim=0).max().item() < 1e-9 * w[0].item()
