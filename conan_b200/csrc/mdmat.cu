@@ -223,11 +223,13 @@ __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, co
     }
     // two j atoms per trip, combined with the three-input minimum; slots past cj repeat atom 0 of
     // the residue (prep_slots_kernel) and kpad is a multiple of 4, so the odd trip reads valid data
+    const float* jx = aJ;                  // three plane pointers walked two atoms at a time
+    const float* jy = aJ + pstride;
+    const float* jz = aJ + 2 * pstride;
 #pragma unroll 1
-    for (int b = 0; b < cj; b += 2) {
-        const float bx = aJ[b * kTile] + Dx, by = aJ[pstride + b * kTile] + Dy, bz = aJ[2 * pstride + b * kTile] + Dz;
-        const float cx = aJ[(b + 1) * kTile] + Dx, cy = aJ[pstride + (b + 1) * kTile] + Dy,
-                    cz = aJ[2 * pstride + (b + 1) * kTile] + Dz;
+    for (int b = 0; b < cj; b += 2, jx += 2 * kTile, jy += 2 * kTile, jz += 2 * kTile) {
+        const float bx = jx[0] + Dx, by = jy[0] + Dy, bz = jz[0] + Dz;
+        const float cx = jx[kTile] + Dx, cy = jy[kTile] + Dy, cz = jz[kTile] + Dz;
         const float nb = fmaf(bz, bz, fmaf(by, by, bx * bx));
         const float nc = fmaf(cz, cz, fmaf(cy, cy, cx * cx));
         const f32x2 BX = pack2(bx, bx), BY = pack2(by, by), BZ = pack2(bz, bz), NB = pack2(nb, nb);
