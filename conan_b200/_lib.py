@@ -50,6 +50,8 @@ SIGNATURES = {
                                                c_void_p, c_void_p]),
     "conan_write_matrices": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32, c_i32, c_i32,
                                             c_void_p, c_i32, c_i32, c_void_p, c_void_p, ctypes.c_char_p, c_i32]),
+    "conan_write_pair_table": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_char_p, c_i32, c_i32, c_i32, c_i32, c_void_p, c_i32,
+                                              ctypes.c_char_p, c_i32]),
     "conan_write_xpm": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i32, c_i32, c_i32, c_void_p, ctypes.c_char_p,
                                        ctypes.c_char_p, ctypes.c_char_p, c_i32, c_i32, ctypes.c_char_p, c_i32, c_i32]),
     "conan_mdmat_workspace_bytes": (c_size, [c_i64, c_i32, c_i32, c_i32]),

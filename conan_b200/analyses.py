@@ -11,7 +11,7 @@ import os
 
 import numpy as np
 
-from . import stage3
+from . import stage3, tables
 
 
 # ------------------------------------------------------------------------------------------------
@@ -89,11 +89,9 @@ class _Ctx:
         return self.layout.to_matrix(per_pair, diag=diag)
 
     def write_map(self, path, mat, fmt="%4d %4d %10.6f\n"):
-        lay = self.layout
-        with open(path, "w") as f:
-            for i in range(lay.xres):
-                f.write("".join(fmt % ((i + lay.xterm, j + lay.yterm) + tuple(np.atleast_1d(mat[i, j]))) for j in range(lay.yres)))
-                f.write("\n")
+        mat = np.asarray(mat)
+        cols = [mat] if mat.ndim == 2 else [mat[:, :, c] for c in range(mat.shape[2])]
+        tables.write_pair_table(path, self.layout, cols, fmt)
 
     def varying(self, frame_mask=None):
         """len(set(rvec)) > 1 for every pair, exactly: lowest and highest level differ as float16 values."""
@@ -141,11 +139,7 @@ def pearson_obs(ctx, path, ignore_time=False):
         trio = np.stack([np.where(ok, res[n][k], 0.0) for n in ("r", "slope", "stderr")], axis=-1)   # [P, 3]
         lay = ctx.layout
         mats = [lay.to_matrix(trio[:, c], diag=0.0) for c in range(3)]
-        with open("aggregate/pearson_data_obs_%d.dat" % (k + 1), "w") as f:
-            for i in range(lay.xres):
-                f.write("".join("%4d %4d %10.6f %10.6f %10.6f\n" % (i + lay.xterm, j + lay.yterm, mats[0][i, j], mats[1][i, j], mats[2][i, j])
-                                for j in range(lay.yres)))
-                f.write("\n")
+        tables.write_pair_table("aggregate/pearson_data_obs_%d.dat" % (k + 1), lay, mats, "%4d %4d %10.6f %10.6f %10.6f\n")
         out.append(trio)
     return out
 

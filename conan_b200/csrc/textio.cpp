@@ -228,3 +228,93 @@ extern "C" int conan_write_xpm(const uint16_t* h_levels, int64_t levels_stride, 
     close(fd);
     return rc;
 }
+
+// ---------------------------------------------------------------------------------------------
+// residue-pair tables: one row per (i, j), a blank line after each i (the layout of
+// aggregate/timeline.dat, mdmat_average_rmsf.dat, pearson_data.dat, pca/pc.N.dat, cluster maps ...)
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct Piece {
+    std::string fmt;   // one printf conversion with the literal text that follows it
+    bool integer;
+};
+
+// Split a printf row format into its conversions; integer conversions are widened to long long.
+bool split_format(const char* format, std::vector<Piece>* out) {
+    const std::string f(format);
+    size_t pos = f.find('%');
+    if (pos != 0) return false;
+    while (pos != std::string::npos) {
+        size_t next = f.find('%', pos + 1);
+        std::string piece = f.substr(pos, next == std::string::npos ? std::string::npos : next - pos);
+        // conversion character: first letter after the flags / width / precision
+        size_t c = 1;
+        while (c < piece.size() && std::strchr("-+ #0123456789.", piece[c])) c++;
+        if (c >= piece.size()) return false;
+        Piece p;
+        const char conv = piece[c];
+        if (conv == 'd' || conv == 'i') {
+            p.integer = true;
+            piece = piece.substr(0, c) + "lld" + piece.substr(c + 1);
+        } else if (conv == 'f' || conv == 'e' || conv == 'g' || conv == 'E' || conv == 'G') {
+            p.integer = false;
+        } else {
+            return false;
+        }
+        p.fmt = piece;
+        out->push_back(p);
+        pos = next;
+    }
+    return true;
+}
+
+}  // namespace
+
+extern "C" int conan_write_pair_table(const char* path, const char* header, int32_t xterm, int32_t xres, int32_t yterm,
+                                      int32_t yres, const double* const* columns, int32_t ncol, const char* row_format,
+                                      int32_t nthreads) {
+    if (!path || !row_format || xres <= 0 || yres <= 0 || ncol < 0 || (ncol > 0 && !columns))
+        return fail(CONAN_ERR_ARG, "conan_write_pair_table: bad arguments");
+    std::vector<Piece> pieces;
+    if (!split_format(row_format, &pieces) || (int)pieces.size() != ncol + 2 || !pieces[0].integer || !pieces[1].integer)
+        return fail(CONAN_ERR_ARG, "conan_write_pair_table: row format \"%s\" does not hold two integer and %d value conversions",
+                    row_format, ncol);
+    std::vector<std::string> ytext(yres);
+    {
+        char b[64];
+        for (int j = 0; j < yres; j++) {
+            snprintf(b, sizeof b, pieces[1].fmt.c_str(), (long long)(yterm + j));
+            ytext[j] = b;
+        }
+    }
+    std::vector<std::string> blocks(xres);
+    const int rc = run_frames(xres, nthreads, [&](int64_t i) -> int {
+        char b[96];
+        snprintf(b, sizeof b, pieces[0].fmt.c_str(), (long long)(xterm + i));
+        const std::string itext(b);
+        std::string& text = blocks[i];
+        text.reserve((size_t)yres * (itext.size() + 8 + 14 * (size_t)ncol) + 1);
+        for (int j = 0; j < yres; j++) {
+            text += itext;
+            text += ytext[j];
+            const int64_t e = i * yres + j;
+            for (int c = 0; c < ncol; c++) {
+                const double v = columns[c][e];
+                if (pieces[c + 2].integer) snprintf(b, sizeof b, pieces[c + 2].fmt.c_str(), (long long)v);
+                else snprintf(b, sizeof b, pieces[c + 2].fmt.c_str(), v);
+                text += b;
+            }
+        }
+        text += '\n';
+        return CONAN_OK;
+    });
+    if (rc != CONAN_OK) return rc;
+    const int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) return fail(CONAN_ERR_IO, "cannot open %s: %s", path, strerror(errno));
+    bool ok = true;
+    if (header && *header) ok = write_all(fd, header, strlen(header), 0, false);
+    for (int i = 0; ok && i < xres; i++) ok = write_all(fd, blocks[i].data(), blocks[i].size(), 0, false);
+    close(fd);
+    return ok ? CONAN_OK : fail(CONAN_ERR_IO, "short write to %s", path);
+}

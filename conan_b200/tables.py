@@ -44,6 +44,20 @@ class Layout:
         return pi + self.xterm, pj + self.yterm
 
 
+def write_pair_table(path, layout, columns, row_format, header=""):
+    """One row per residue pair and a blank line after each x residue, formatted by the native threaded
+    writer (conan_write_pair_table).  columns: [xres, yres] arrays, one per value conversion of row_format."""
+    import ctypes
+    import os
+    from . import _lib
+    cols = [np.ascontiguousarray(c, dtype=np.float64).reshape(layout.xres * layout.yres) for c in columns]
+    ptrs = (ctypes.c_void_p * max(len(cols), 1))(*[c.ctypes.data for c in cols])
+    lib = _lib.load()
+    _lib.check(lib.conan_write_pair_table(os.fsencode(path), header.encode(), layout.xterm, layout.xres, layout.yterm,
+                                          layout.yres, ptrs, len(cols), row_format.encode(),
+                                          min(32, os.cpu_count() or 1)))
+
+
 class Stage2Tables:
     """Everything read_process_frames derives after its frame loop."""
 
@@ -128,19 +142,14 @@ class Stage2Tables:
         avg = lay.to_matrix(self.avg, diag=0.0)
         std = lay.to_matrix(self.std, diag=0.0)
         span = self.tmax - self.t0
-        with open(directory + "/timeline.dat", "w") as ft, open(directory + "/mdmat_average_rmsf.dat", "w") as fa:
-            ft.write("#  i  j   t_first t_last t_total (# encounters)\n")
-            ft.write("# first/last time residues i and j are within the interaction distance.\n")
-            ft.write("# total: fraction of frames in which residues i and j are within interaction distance (maximum = 1.0).\n")
-            fa.write("#  i  j  r_ij^avg sigma_(rij)\n")
-            fa.write("# average of the distance between residues i and j and the standard deviation (computed across frames.\n")
-            for i in range(lay.xres):
-                ii = i + lay.xterm
-                ft.write("".join("%4d %4d %12i %12i %12.6f %12.6f %5i\n" % (ii, j + lay.yterm, first[i, j], last[i, j], life[i, j], span, nenc[i, j])
-                                 for j in range(lay.yres)))
-                fa.write("".join("%4d %4d %9.4f %9.4f\n" % (ii, j + lay.yterm, avg[i, j], std[i, j]) for j in range(lay.yres)))
-                ft.write("\n")
-                fa.write("\n")
+        write_pair_table(directory + "/timeline.dat", lay, [first, last, life, np.full_like(life, span), nenc],
+                         "%4d %4d %12i %12i %12.6f %12.6f %5i\n",
+                         "#  i  j   t_first t_last t_total (# encounters)\n"
+                         "# first/last time residues i and j are within the interaction distance.\n"
+                         "# total: fraction of frames in which residues i and j are within interaction distance (maximum = 1.0).\n")
+        write_pair_table(directory + "/mdmat_average_rmsf.dat", lay, [avg, std], "%4d %4d %9.4f %9.4f\n",
+                         "#  i  j  r_ij^avg sigma_(rij)\n"
+                         "# average of the distance between residues i and j and the standard deviation (computed across frames.\n")
         with open(directory + "/native_contacts.dat", "w") as f:
             f.write("# time (ns)  #native #non-native\n")
             for t, a, b in zip(self.time_vec, self.native, self.nonnative):

@@ -307,6 +307,17 @@ int conan_write_xpm(const uint16_t* h_levels, int64_t levels_stride, int64_t nf,
                     const char* codes, int32_t nchar, int32_t nlevels, const char* path, int32_t append,
                     int32_t nthreads);
 
+/* A residue-pair table: `header`, then one row per pair (x residue i outer, y residue j inner) and a
+ * blank line after each i -- the layout of aggregate/timeline.dat and mdmat_average_rmsf.dat
+ * (conan.py:917, :926), pearson_data.dat (:1916), pca/pc.N.dat (:428), the cluster maps (:1316-1326).
+ * row_format is the reference's printf row format: two integer conversions for the residue numbers
+ * (xterm + i, yterm + j), then one conversion per column (%d / %i columns print the value truncated to
+ * an integer, as Python's % does with floats), ending in "\n".  columns[c] is [xres * yres] float64,
+ * x-major.  Rows are formatted on nthreads host threads. */
+int conan_write_pair_table(const char* path, const char* header, int32_t xterm, int32_t xres, int32_t yterm,
+                           int32_t yres, const double* const* columns, int32_t ncol, const char* row_format,
+                           int32_t nthreads);
+
 /* ------------------------------------------------------------------------------------ */
 /* Measurement helpers (bench.py only).                                                  */
 /* ------------------------------------------------------------------------------------ */

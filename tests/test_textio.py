@@ -112,3 +112,30 @@ def test_writer_errors(tmp_path):
     rc = lib.conan_write_matrices(stack.ctypes.data, 64, 1, 0, 1, 1, 3, 1, 4, values.ctypes.data, 11, 0, None, None,
                                   os.fsencode(str(tmp_path)), 1)
     assert rc == -1
+
+
+def test_pair_table_matches_python_formatting(tmp_path):
+    rng = np.random.default_rng(8)
+    lay = tables.Layout(xterm=3, xres=5, yterm=40, yres=7)
+    a = rng.normal(0, 50, size=(5, 7))
+    b = rng.integers(-5, 2000000, size=(5, 7)).astype(np.float64) + 0.75      # printed with %12i: truncated
+    c = rng.uniform(0, 1, size=(5, 7))
+    c[1, 2] = 0.1234565                                                         # a rounding tie in binary terms
+    c[0, 0] = -0.0
+    fmt = "%4d %4d %12i %12.6f %9.4f\n"
+    head = "# a header\n# of two lines\n"
+    path = tmp_path / "t.dat"
+    tables.write_pair_table(str(path), lay, [b, a, c], fmt, head)
+    want = head
+    for i in range(5):
+        for j in range(7):
+            want += fmt % (i + 3, j + 40, b[i, j], a[i, j], c[i, j])
+        want += "\n"
+    assert path.read_text() == want
+    # no value columns, and a format the writer must refuse
+    tables.write_pair_table(str(path), lay, [], "%5i %5i\n")
+    assert path.read_text().splitlines()[0] == "%5i %5i" % (3, 40)
+    with pytest.raises(_lib.ConanError):
+        tables.write_pair_table(str(path), lay, [a], "%4d %4d %s\n")
+    with pytest.raises(_lib.ConanError):
+        tables.write_pair_table(str(path), lay, [a, c], "%4d %4d %9.4f\n")
