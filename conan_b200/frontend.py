@@ -536,6 +536,56 @@ def write_matrix(outputf, time, xterm, xres, yterm, yres, trunc, dict_frame, dr,
         outputf.write("\n")
 
 
+class LazyVectors:
+    """The reference's `vectors` (conan.py:731, :821-826): float16 distances [pairs seen, frames].
+
+    The data lives on the GPU as the level stack; this object gathers the seen pairs' columns, maps
+    levels to float16 distances and transposes on the device, and copies the result to the host the first
+    time the array is actually looked at (np.asarray(v), v[i], v.T, any ndarray attribute).  A run that
+    never touches `vectors` (the command-line path works on the device stack) never pays for the copy."""
+
+    def __init__(self, d_stack, seen, values):
+        self._d_stack, self._seen, self._values = d_stack, np.asarray(seen, dtype=np.int64), np.asarray(values)
+        self._host = None
+        self.shape = (len(self._seen), int(d_stack.shape[0]))
+        self.dtype = np.dtype(np.float16)
+        self.ndim = 2
+
+    def _materialise(self):
+        if self._host is None:
+            import torch
+            d_stack, dev = self._d_stack, self._d_stack.device
+            nsel, nf = self.shape
+            out = np.empty((nsel, nf), dtype=np.float16)
+            lut = torch.from_numpy(self._values.astype(np.float16)).to(dev)
+            d_sel = torch.from_numpy(self._seen).to(dev)
+            chunk = max(1, int(2.0e8 // max(nf, 1)))
+            for c0 in range(0, nsel, chunk):
+                cols = d_stack.view(torch.int16).index_select(1, d_sel[c0:c0 + chunk]).to(torch.int64) & 0xffff
+                out[c0:c0 + chunk] = lut[cols].T.contiguous().cpu().numpy()
+            self._host = out
+            self._d_stack = None
+        return self._host
+
+    def __array__(self, dtype=None, copy=None):
+        a = self._materialise()
+        return a if dtype is None else a.astype(dtype)
+
+    def __len__(self):
+        return self.shape[0]
+
+    def __getitem__(self, idx):
+        return self._materialise()[idx]
+
+    def __iter__(self):
+        return iter(self._materialise())
+
+    def __getattr__(self, name):          # everything else an ndarray offers
+        if name.startswith("_"):
+            raise AttributeError(name)
+        return getattr(self._materialise(), name)
+
+
 def _write_matrix_files(levels_host, values, layout, trunc, dr_mode, nframes, symmetric):
     """matrices/%05d.dat (+ _dr.init / _dr.prev) straight from the level stack (conan_write_matrices)."""
     lay = layout
@@ -662,8 +712,7 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
     if economy:
         vectors = np.zeros((0, 0), dtype=np.float16)
     else:
-        lut16 = values.astype(np.float16)
-        vectors = np.ascontiguousarray(lut16[host_levels()[:, seen]].T)
+        vectors = LazyVectors(d_stack, seen, values)
 
     if interact_pair_dict:
         life = layout.to_matrix(tab.lifetime, diag=-1.0)

@@ -257,3 +257,41 @@ def test_begin_end_dt_select_frames(lib, orc, goldens, tmp_path):
     nc = np.loadtxt(str(tmp_path / "aggregate" / "native_contacts.dat"))
     assert np.array_equal(nc[:, 0], np.array([200.0, 400.0, 600.0, 800.0]))
     assert np.array_equal(nc[:, 1], want["native"]) and np.array_equal(nc[:, 2], want["nonnative"])
+
+
+@pytest.mark.parametrize("case", ["hyst", "asym"])
+def test_import_api_return_tuple(lib, tmp_path, case):
+    """`import conan` users: read_index + read_process_frames with the reference's signature and return
+    tuple (conan.py:697, :1021-1023), `vectors` included (it is gathered from the GPU stack on first use)."""
+    from conan_b200 import frontend, xpm
+    c = np.load(os.path.join(GOLDEN, "case_%s.npz" % case))
+    full, times = c["in/levels_full"], c["in/times"]
+    trunc, nlevels = float(c["in/trunc"]), int(c["in/nlevels"])
+    cwd = os.getcwd()
+    os.chdir(str(tmp_path))
+    try:
+        with open("dmf.xpm", "w") as f:
+            xpm.write_xpm(f, full, times, trunc, nlevels)
+        nres = full.shape[1]
+        asymm_data = None
+        if case == "asym":
+            xdict = {m: m for m in range(1, 6)}
+            ydict = {m: m for m in range(6, 13)}
+            asymm_data = (xdict, ydict, 5, 7, 1, 6)
+        with open("dmf.xpm") as inputf:
+            nres_r, nlevels_r, nchar, dict_legend, trunc_r = frontend.read_index(inputf)
+            assert (nres_r, nlevels_r) == (nres, nlevels) and abs(trunc_r - trunc) < 1e-6
+            ret = frontend.read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, trunc, 0.5, 0.6,
+                                               None, None, None, False, None, 0, None, False, False, False, None,
+                                               [], None, 0.5, matrices=False)
+    finally:
+        os.chdir(cwd)
+    begin, dt, time_vec, pairs_list, pairs_legend, vectors = ret[:6]
+    assert np.array_equal(time_vec, c["ret/time_vec"])
+    want_pairs = [tuple(p) for p in c["ret/pairs_list"]]
+    assert sorted(pairs_list) == sorted(want_pairs)
+    assert vectors.shape == c["ret/vectors"].shape and vectors.dtype == np.float16
+    got = np.asarray(vectors)
+    order = [pairs_legend[p] for p in want_pairs]        # the reference lists pairs in order of first appearance
+    assert np.array_equal(got[order], c["ret/vectors"])
+    assert np.array_equal(vectors[order[0]], c["ret/vectors"][0]) and len(vectors) == len(want_pairs)
