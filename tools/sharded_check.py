@@ -55,6 +55,38 @@ def main():
             ok &= same
             print("%-10s %s" % (k, "ok" if same else "MISMATCH"))
         print("sharded_check world=%d: %s (n_enc max %d)" % (world, "PASS" if ok else "FAIL", int(ref["n_enc"].max())))
+
+    # ---- stage 3 on the shards: covariance (contraction over frames, all-reduce) and frame-frame rows ----
+    from conan_b200 import stage3
+    values = legend_values(trunc, nlevels)
+    lut = stage3.lut16(values, dev)
+    merged = st.host()
+    lut_h = np.asarray(values).astype(np.float16)
+    shift = lut_h[np.clip(np.rint(merged["sum_k"] / nf).astype(np.int64), 0, nlevels - 1)].astype(np.float32)
+    mean, nf_total = sharded.global_mean(mine, geom.P, nlevels, lut, shift)
+    lo_level = np.empty(geom.P, np.int64)
+    kmin, _ = stage3.level_range(mine, geom.P)
+    t_kmin = torch.from_numpy(np.asarray(kmin, np.int64)).to(dev)
+    dist.all_reduce(t_kmin, op=dist.ReduceOp.MIN)
+    sel = np.flatnonzero(t_kmin.cpu().numpy() < nlevels - 1).astype(np.int32)        # pairs ever below trunc
+    cov = sharded.covariance_sharded(mine, sel, nlevels, lut, mean[sel], nf_total)
+    norm = nres / np.sqrt(2.0)
+    block, row0 = sharded.frame_distances_sharded(mine, sel, nlevels, lut, mean[sel], norm)
+    torch.cuda.synchronize(dev)
+    if rank == 0:
+        full_mean = stage3.linregress_all(whole, geom.P, nlevels, lut, np.zeros((1, nf)), shift)["mean"]
+        ok3 = nf_total == nf and np.abs(full_mean - mean).max() < 1e-12
+        cov1 = stage3.covariance(whole, sel, nlevels, lut, full_mean[sel])
+        e_cov = (torch.linalg.norm((cov - cov1).double()) / torch.linalg.norm(cov1.double())).item()
+        d1 = stage3.frame_distances(whole, sel, nlevels, lut, full_mean[sel], norm)
+        e_d = (torch.linalg.norm((block - d1[row0:row0 + block.shape[0]]).double()) / torch.linalg.norm(d1[:block.shape[0]].double())).item()
+        # and against float64 numpy on the float16 vectors
+        vec = lut_h[whole.view(torch.int16).cpu().numpy().view(np.uint16)[:, sel]].astype(np.float64).T
+        e_np = np.linalg.norm(cov.cpu().numpy() - np.cov(vec)) / np.linalg.norm(np.cov(vec))
+        ok3 &= e_cov < 2e-6 and e_d < 2e-6 and e_np < 1e-5
+        print("stage 3 shards: %d pairs; covariance vs one GPU %.2e, vs numpy float64 %.2e; frame-frame rows vs one GPU %.2e: %s"
+              % (len(sel), e_cov, e_np, e_d, "PASS" if ok3 else "FAIL"))
+        ok &= ok3
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
