@@ -56,22 +56,37 @@ __host__ __device__ inline int round_up(int v, int m) { return (v + m - 1) / m *
 // ------------------------------------------------------------------------------------------
 // prep: slots + bounding spheres
 // ------------------------------------------------------------------------------------------
+// Inside every block of 64 residues the tile kernel wants the residues ordered by their number of
+// atoms: threads of a warp then work on residue pairs of similar size and run the same number of
+// loop trips (residue sizes differ by a factor of three in a protein).  perm[position] = residue.
+__global__ void block_perm_kernel(const int* __restrict__ res_start, int nres, int* __restrict__ perm) {
+    __shared__ int s_cnt[kTile];
+    const int l = threadIdx.x, r = blockIdx.x * kTile + l;
+    const int n = r < nres ? res_start[r + 1] - res_start[r] : 0x7fffffff;     // padding sorts last
+    s_cnt[l] = n;
+    __syncthreads();
+    int pos = 0;
+    for (int k = 0; k < kTile; k++) pos += (s_cnt[k] < n || (s_cnt[k] == n && k < l)) ? 1 : 0;
+    perm[blockIdx.x * kTile + pos] = r;
+}
+
 __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __restrict__ res_start,
-                                  int64_t nf, int natoms, int nres, int nres_pad, int kpad,
-                                  float* __restrict__ slots, float4* __restrict__ sph,
+                                  const int* __restrict__ perm, int64_t nf, int natoms, int nres, int nres_pad,
+                                  int kpad, float* __restrict__ slots, float4* __restrict__ sph,
                                   int* __restrict__ cnt) {
     int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= nf * nres_pad) return;
     int64_t f = gid / nres_pad;
-    int r = (int)(gid - f * nres_pad);
+    const int pos = (int)(gid - f * nres_pad);         // position in the padded, per-block sorted order
+    const int r = perm[pos];                            // the residue that sits there
     const size_t kstride = (size_t)nres_pad;
     const size_t pstride = (size_t)kpad * nres_pad;
-    float* sl = slots + (size_t)f * kPlanes * pstride + r;
+    float* sl = slots + (size_t)f * kPlanes * pstride + pos;
     if (r >= nres) {
         for (int pl = 0; pl < kPlanes; pl++)
             for (int k = 0; k < kpad; k++) sl[pl * pstride + k * kstride] = 0.f;
-        sph[(size_t)f * nres_pad + r] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (f == 0) cnt[r] = 0;
+        sph[(size_t)f * nres_pad + pos] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (f == 0) cnt[pos] = 0;
         return;
     }
     const int a0 = res_start[r], a1 = res_start[r + 1];
@@ -92,8 +107,8 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
         o[3 * pstride] = -2.f * px; o[4 * pstride] = -2.f * py; o[5 * pstride] = -2.f * pz;
         o[6 * pstride] = n2;
     }
-    sph[(size_t)f * nres_pad + r] = make_float4(cx, cy, cz, sqrtf(r2max) * 1.000001f);
-    if (f == 0) cnt[r] = n;
+    sph[(size_t)f * nres_pad + pos] = make_float4(cx, cy, cz, sqrtf(r2max) * 1.000001f);
+    if (f == 0) cnt[pos] = n;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -147,6 +162,7 @@ struct MdmatParams {
     const float4* sph;       // [nf][nres_pad]
     const int* cnt;          // [nres_pad]
     const int* res_start;    // [nres + 1] (device copy)
+    const int* perm;         // [nres_pad] residue at each position (sorted by size inside blocks of 64)
     const float* xyz;        // [nf][natoms][3] original coordinates (exact path)
     const float* box;        // [nf][9] or nullptr
     const float* slots;      // [nf][7][kpad][nres_pad], for the plain-load debug path
@@ -362,7 +378,9 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     uint16_t* slow = list + kListCap;                                     // [kSlowCap]
     uint64_t* bar = reinterpret_cast<uint64_t*>(slow + kSlowCap);
     int* counters = reinterpret_cast<int*>(bar + 1);   // [0] list [1] redo list [2] near [3] evals [4] survivors
-    int* rowbase = counters + 6;                        // [64] element index of pair (gi0 + i, gj0) in a frame row
+    int* rowbase = counters + 6;                        // [64] element index of pair (row residue, residue 0) in a frame row
+    int* origI = rowbase + kTile;                       // [64] residue at row position i / column position j of the tile
+    int* origJ = origI + kTile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t blk = blockIdx.x;
@@ -442,7 +460,9 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         }
         (isI ? grpI : grpJ)[l] = make_float4(s0.x, s0.y, s0.z, R);
         (isI ? cntI : cntJ)[l] = prm.cnt[gr];
-        if (isI) rowbase[l] = pair_idx(gr, gj0);
+        const int res = prm.perm[gr];
+        (isI ? origI : origJ)[l] = res;
+        if (isI) rowbase[l] = pair_idx(res, 0);          // + column residue = the pair's element index
     }
 
     // ---- fill: every pair of the tile starts at the "beyond trunc" level -------------------
@@ -511,10 +531,10 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                     const float* b = prm.box + 9 * (f0 + g);
                     Lx = b[0]; Ly = b[4]; Lz = b[8];
                 }
-                level = exact_pair(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, near);
+                level = exact_pair(prm, f0 + g, origI[i], origJ[j], Lx, Ly, Lz, near);
             }
             if (level < maxlevel)
-                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + j] = (uint16_t)level;
+                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + origJ[j]] = (uint16_t)level;
         }
         __syncthreads();
         const int nslow = min(counters[1], kSlowCap);
@@ -526,9 +546,9 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 const float* b = prm.box + 9 * (f0 + g);
                 Lx = b[0]; Ly = b[4]; Lz = b[8];
             }
-            const int level = exact_pair_warp(prm, f0 + g, gi0 + i, gj0 + j, Lx, Ly, Lz, lane, near);
+            const int level = exact_pair_warp(prm, f0 + g, origI[i], origJ[j], Lx, Ly, Lz, lane, near);
             if (lane == 0)
-                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + j] = (uint16_t)level;
+                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + origJ[j]] = (uint16_t)level;
         }
         near = __reduce_add_sync(0xffffffffu, near);
         evals = __reduce_add_sync(0xffffffffu, evals);
@@ -551,46 +571,54 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             const float* b = prm.box + 9 * (f0 + g);
             Lx = b[0]; Ly = b[4]; Lz = b[8];
         }
-        float4 sj[2];
-        float rjp[2];   // (Rj + trunc/2) * slack: the j half of the pruning distance
-        bool jok[2];
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-            const int j = lane + 32 * h;
-            sj[h] = sJ[j];
-            rjp[h] = (sj[h].w + half_trunc) * kPruneSlack;
-            jok[h] = gj0 + j >= j_beg && gj0 + j < j_end;
-        }
+        // The tile is taken in 16 x 16 sub-blocks, two per warp.  Rows and columns are sorted by residue
+        // size (block_perm_kernel), so the pairs of a sub-block have similar numbers of atoms on both
+        // sides; a sub-block's survivors go into the list as one contiguous run (one reservation), and the
+        // 32 lanes that later take 32 consecutive entries run the same number of loop trips.
 #pragma unroll 1
-        for (int ii = 0; ii < kTile / kWarps; ii++) {
-            const int i = warp * (kTile / kWarps) + ii;
-            const float4 si = sI[i];
-            const bool iok = gi0 + i >= i_beg && gi0 + i < i_end;
-            const float rip = (si.w + half_trunc) * kPruneSlack;
+        for (int sb = warp; sb < 16; sb += kWarps) {
+            const int rb = (sb >> 2) * 16, cb = (sb & 3) * 16;
+            const int j = cb + (lane & 15);
+            const float4 sj = sJ[j];
+            const float rjp = (sj.w + half_trunc) * kPruneSlack;   // the j half of the pruning distance
+            const int jres = origJ[j];
+            const bool jok = jres >= j_beg && jres < j_end;
+            unsigned keepbits = 0, genbits = 0, total = 0;
+            unsigned before[8];          // survivors of the sub-block ahead of this lane's k-th pair
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const int j = lane + 32 * h;
-                float dx = si.x - sj[h].x, dy = si.y - sj[h].y, dz = si.z - sj[h].z;
+            for (int k = 0; k < 8; k++) {
+                const int i = rb + (lane >> 4) + 2 * k;
+                const float4 si = sI[i];
+                const int ires = origI[i];
+                const bool iok = ires >= i_beg && ires < i_end;
+                float dx = si.x - sj.x, dy = si.y - sj.y, dz = si.z - sj.z;
                 bool general = false;
                 if (PBC) {
                     // one lattice shift serves every atom pair only if the spheres stay inside half a box
-                    const float rr = si.w + sj[h].w;
+                    const float rr = si.w + sj.w;
                     dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz);
                     general = !(fabsf(dx) + rr < 0.49999f * Lx && fabsf(dy) + rr < 0.49999f * Ly &&
                                 fabsf(dz) + rr < 0.49999f * Lz);
                 }
                 const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                const float T = rip + rjp[h];
-                const bool keep = iok && jok[h] && (!diag || j > i) && !(d2 > T * T);
+                const float T = (si.w + half_trunc) * kPruneSlack + rjp;
+                const bool keep = iok && jok && (!diag || jres > ires) && !(d2 > T * T);
                 const unsigned ball = __ballot_sync(0xffffffffu, keep);
-                if (ball) {
-                    int base = 0;
-                    if (lane == 0) base = atom_add_shared(&counters[0], __popc(ball));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (keep)
-                        list[base + __popc(ball & ((1u << lane) - 1))] =
-                            (uint16_t)(i | (j << 6) | (general ? 0x1000 : 0) | (PBC ? (g << 13) : 0));
-                }
+                before[k] = total + __popc(ball & ((1u << lane) - 1));
+                total += __popc(ball);
+                keepbits |= (keep ? 1u : 0u) << k;
+                genbits |= (general ? 1u : 0u) << k;
+            }
+            if (total) {
+                int base = 0;
+                if (lane == 0) base = atom_add_shared(&counters[0], (int)total);
+                base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    if ((keepbits >> k) & 1u) {
+                        const int i = rb + (lane >> 4) + 2 * k;
+                        list[base + before[k]] = (uint16_t)(i | (j << 6) | (((genbits >> k) & 1u) ? 0x1000 : 0) | (PBC ? (g << 13) : 0));
+                    }
             }
         }
         __syncthreads();
@@ -609,7 +637,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
 // ------------------------------------------------------------------------------------------
 struct Layout {
     int nres_pad, kpad;
-    size_t off_res_start, off_cnt, off_sph, off_slots, total;
+    size_t off_res_start, off_cnt, off_perm, off_sph, off_slots, total;
 };
 
 inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -621,6 +649,7 @@ bool make_layout(int64_t nf, int nres, int max_res_atoms, Layout* L) {
     size_t o = 0;
     L->off_res_start = o; o = align256(o + sizeof(int) * (size_t)(nres + 1));
     L->off_cnt = o;       o = align256(o + sizeof(int) * (size_t)L->nres_pad);
+    L->off_perm = o;      o = align256(o + sizeof(int) * (size_t)L->nres_pad);
     L->off_sph = o;       o = align256(o + sizeof(float4) * (size_t)nf * L->nres_pad);
     L->off_slots = o;     o = align256(o + sizeof(float) * (size_t)nf * kPlanes * L->kpad * L->nres_pad);
     L->total = o;
@@ -633,7 +662,7 @@ size_t mdmat_smem_bytes(int kpad, int fb) {
     s += (size_t)(fb + 1) * 2 * kTile * sizeof(float4);         // per-frame and per-group spheres
     s += 2 * kTile * sizeof(int);                               // counts
     s += (size_t)(kListCap + kSlowCap) * sizeof(uint16_t);      // survivor and redo lists
-    s += 8 + 6 * sizeof(int) + kTile * sizeof(int);             // mbarrier + counters + row bases
+    s += 8 + 6 * sizeof(int) + 3 * kTile * sizeof(int);         // mbarrier + counters + row bases + residue numbers
     return (s + 15) & ~(size_t)15;
 }
 
@@ -718,16 +747,18 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
     char* w = static_cast<char*>(d_work);
     int* d_res_start = reinterpret_cast<int*>(w + L.off_res_start);
     int* d_cnt = reinterpret_cast<int*>(w + L.off_cnt);
+    int* d_perm = reinterpret_cast<int*>(w + L.off_perm);
     float4* d_sph = reinterpret_cast<float4*>(w + L.off_sph);
     float* d_slots = reinterpret_cast<float*>(w + L.off_slots);
 
     if (phases & 1) {
         CONAN_CUDA_TRY(cudaMemcpyAsync(d_res_start, h_res_start, sizeof(int) * (size_t)(nres + 1),
                                        cudaMemcpyHostToDevice, stream));
+        block_perm_kernel<<<(unsigned)(L.nres_pad / kTile), kTile, 0, stream>>>(d_res_start, nres, d_perm);
         const int64_t total = nf * L.nres_pad;
         const int threads = 128;
         prep_slots_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, stream>>>(
-            d_xyz, d_res_start, nf, natoms, nres, L.nres_pad, L.kpad, d_slots, d_sph, d_cnt);
+            d_xyz, d_res_start, d_perm, nf, natoms, nres, L.nres_pad, L.kpad, d_slots, d_sph, d_cnt);
         CONAN_CUDA_TRY(cudaGetLastError());
     }
     if (!(phases & 2)) return CONAN_OK;
@@ -741,7 +772,7 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
     CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 
     MdmatParams prm;
-    prm.cnt = d_cnt; prm.res_start = d_res_start; prm.counters = d_counters;
+    prm.cnt = d_cnt; prm.res_start = d_res_start; prm.perm = d_perm; prm.counters = d_counters;
     prm.natoms = natoms; prm.nres = nres; prm.nres_pad = L.nres_pad; prm.kpad = L.kpad; prm.fb = fb;
     prm.symmetric = symmetric ? 1 : 0;
     prm.x0 = x0; prm.xres = xres; prm.y0 = y0; prm.yres = yres;

@@ -8,6 +8,8 @@ call's leftovers -- and requires the level stacks to equal conan_mdmat_frames' b
 lives in the last-collected test file so a run that stops at the first failure has already run
 everything else, and it must also pass on its own in a fresh process.
 """
+import gc
+
 import numpy as np
 import pytest
 
@@ -28,11 +30,17 @@ def _both_entry_points(xyz, boxes, geom, trunc, nlevels, pbc):
     got = torch.zeros((nf, geom.stride), dtype=torch.uint16, device=dev)
     c_got = torch.zeros(3, dtype=torch.int64, device=dev)
     torch.cuda.synchronize(dev)
-    before = (torch.cuda.memory_allocated(dev), torch.cuda.mem_get_info(dev)[0])
-    stage1.mdmat_frames_static(d_xyz, d_box, geom, trunc, nlevels, pbc, got, c_got)
-    torch.cuda.synchronize(dev)
-    # neither torch's allocator nor the driver saw an allocation during the call
-    assert (torch.cuda.memory_allocated(dev), torch.cuda.mem_get_info(dev)[0]) == before
+    # (tensors left over from earlier tests must not be collected in the middle of the comparison)
+    gc.collect()
+    gc.disable()
+    try:
+        before = (torch.cuda.memory_allocated(dev), torch.cuda.mem_get_info(dev)[0])
+        stage1.mdmat_frames_static(d_xyz, d_box, geom, trunc, nlevels, pbc, got, c_got)
+        torch.cuda.synchronize(dev)
+        # neither torch's allocator nor the driver saw an allocation during the call
+        assert (torch.cuda.memory_allocated(dev), torch.cuda.mem_get_info(dev)[0]) == before
+    finally:
+        gc.enable()
     to_np = lambda t: t.view(torch.int16).cpu().numpy().view(np.uint16)[:, :geom.P]
     return to_np(ref), to_np(got), c_ref.cpu().numpy(), c_got.cpu().numpy()
 
