@@ -45,8 +45,8 @@ constexpr int kMaxKpad = 128;      // largest supported atoms-per-residue (after
 constexpr int kMaxFB = 4;          // frames per CTA at most (2 bits in a list entry)
 constexpr int kPlanes = 7;         // x' y' z' | -2x' -2y' -2z' |a'|^2
 constexpr int kPlanesJ = 3, kPlanesI = 4;
-constexpr int kListCap = 5120;     // survivor list entries (a frame adds at most 4096)
-constexpr int kSlowCap = 1024;     // pairs waiting for the exact path
+constexpr int kListCap = 4608;     // survivor list entries (a frame adds at most 4096)
+constexpr int kSlowCap = 512;      // pairs waiting for the exact path
 constexpr int kSmemBudget = 74 * 1024;   // keeps three CTAs per SM
 constexpr float kPruneSlack = 1.00001f;
 constexpr float kErrC = 64.0f * 5.9604645e-8f;   // rounding bound of the expanded form, see fast_pair()
