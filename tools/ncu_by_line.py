@@ -41,7 +41,7 @@ for l in dis[start + 1:]:
     if m:
         cur_line = int(m.group(1))
         continue
-    if re.match(r"\s+/\*[0-9a-f]{4}\*/", l):
+    if re.match(r"\s+/\*[0-9a-f]{4,6}\*/", l):
         lines.append(cur_line)
 print("sass in ncu %d, in disasm %d" % (len(data), len(lines)))
 n = min(len(data), len(lines))
