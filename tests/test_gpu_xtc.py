@@ -80,3 +80,21 @@ def test_malformed_frames_are_reported(torch_cuda, tmp_path):
     # the other frames still decode
     ids = np.array([0, 1, 3, 4, 5])
     assert np.array_equal(bad.decode_device(frame_ids=ids).cpu().numpy(), x.decode(frame_ids=ids))
+
+
+def test_random_systems(torch_cuda, tmp_path):
+    """Clustered / spread / wide random systems at several precisions: the GPU decoder equals the host decoder."""
+    from conan_b200.xtc import XtcFile, write_xtc
+    rng = np.random.default_rng(11)
+    for case in range(24):
+        natoms = int(rng.integers(10, 400))
+        nframes = int(rng.integers(1, 40))
+        spread = [0.02, 0.3, 3.0, 60.0][case % 4]
+        cluster = [0.0, 0.05, 0.4][case % 3]
+        precision = [10.0, 1000.0, 100000.0][(case // 4) % 3]
+        centres = rng.uniform(-spread, spread, size=(nframes, natoms // 5 + 1, 3))
+        xyz = (centres[:, np.arange(natoms) // 5] + rng.normal(0, cluster, size=(nframes, natoms, 3))).astype(np.float32)
+        p = str(tmp_path / "r.xtc")
+        write_xtc(p, xyz, precision=precision)
+        x = XtcFile(p)
+        assert np.array_equal(x.decode_device().cpu().numpy(), x.decode()), (case, natoms, nframes, spread, cluster, precision)

@@ -82,3 +82,30 @@ def test_truncated_file_is_an_error(lib, tmp_path):
     data = open(os.path.join(GOLDEN, "sample.xtc"), "rb").read()
     with pytest.raises(ConanError):
         XtcFile(data[:-5])
+
+
+def test_encode_decode_property(lib, orc, tmp_path):
+    """Randomised systems (clustered, spread, tiny and wide boxes, several precisions): the encoder's streams are
+    read back identically by the host decoder and by the oracle's independent decoder, within half a quantum
+    of the original coordinates."""
+    from hypothesis import given, settings, strategies as st
+    from conan_b200.xtc import XtcFile, write_xtc
+
+    @settings(max_examples=40, deadline=None)
+    @given(natoms=st.integers(1, 70), nframes=st.integers(1, 3), spread=st.sampled_from([0.02, 0.3, 3.0, 60.0]),
+           cluster=st.sampled_from([0.0, 0.05, 0.4]), precision=st.sampled_from([10.0, 1000.0, 100000.0]),
+           seed=st.integers(0, 2 ** 31 - 1))
+    def check(natoms, nframes, spread, cluster, precision, seed):
+        rng = np.random.default_rng(seed)
+        centres = rng.uniform(-spread, spread, size=(nframes, max(1, natoms // 5 + 1), 3))
+        xyz = centres[:, np.arange(natoms) // 5] + rng.normal(0, cluster, size=(nframes, natoms, 3))
+        xyz = xyz.astype(np.float32)
+        p = str(tmp_path / "h.xtc")
+        write_xtc(p, xyz, precision=precision)
+        x = XtcFile(p)
+        got = x.decode()
+        _, _, oxyz = orc.xtc_decode(open(p, "rb").read())
+        assert np.array_equal(got, oxyz)
+        tol = 0.0 if natoms <= 9 else 0.5 / precision * 1.0001 + np.abs(xyz).max() * 2.0e-7
+        assert np.abs(got.astype(np.float64) - xyz.astype(np.float64)).max() <= tol
+    check()
