@@ -7,6 +7,7 @@ reference leaves to scipy after those contractions -- the top-k eigenpairs (ARPA
 torch.linalg.eigh on the device here) and Ward linkage / fcluster (scipy in both) -- stays a
 library call: small, and outside the hot path.
 """
+import math
 import os
 
 import numpy as np
@@ -144,10 +145,71 @@ def pearson_obs(ctx, path, ignore_time=False):
     return out
 
 
+def _project_pc(ctx, sel, mean, v, change_sign):
+    """project_pc (conan.py:430-452): projections of the float16 mean-free vectors on the columns of v (device,
+    [nsel, n] float64), sign chosen so that a projection does not decrease with time; writes pca_projections.dat."""
+    import torch
+    from scipy.stats import linregress
+    dev = ctx.d_stack.device
+    npc = v.shape[1]
+    d_sel = torch.from_numpy(sel.astype(np.int64)).to(dev)
+    mean16 = torch.from_numpy(mean.astype(np.float32).astype(np.float16)).to(dev)
+    lut16 = ctx.lut.to(torch.float16)
+    proj = torch.empty((ctx.nf, npc), dtype=torch.float64, device=dev)
+    step = max(1, int(2.0e8 // max(len(sel), 1)))
+    for f0 in range(0, ctx.nf, step):
+        lv = ctx.d_stack[f0:f0 + step].view(torch.int16).to(torch.int64) & 0xffff
+        vm0 = (lut16[lv.index_select(1, d_sel)] - mean16[None, :]).double()      # float16 arithmetic, then widened
+        proj[f0:f0 + step] = vm0 @ v
+    proj = proj.cpu().numpy()
+    v = v.cpu().numpy()
+    print("Projecting principal components...")
+    if change_sign:
+        for i in range(npc):
+            if linregress(proj[:, i], ctx.time_vec).rvalue < 0:
+                v[:, i] = -v[:, i]
+                proj[:, i] *= -1
+    with open("pca/pca_projections.dat", "w") as f:
+        for n in range(ctx.nf):
+            f.write("%12i" % ctx.time_vec[n])
+            f.write((npc * " %12.6f") % tuple(proj[n]) + "\n")
+    return v, proj
+
+
+def pca_read(ctx, pca_dir):
+    """PCA_READ: project the trajectory on principal components written by an earlier run
+    (pca/pc.N.dat of that run; conan.py:1073-1095, :2003-2010).  No sign change."""
+    import torch
+    os.makedirs("pca", exist_ok=True)
+    sel = ctx.seen.astype(np.int32)
+    print("There are a total of %i non-constant pairs." % len(sel))
+    lay = ctx.layout
+    pi, pj = lay.pair_labels()
+    cols = []
+    i = 1
+    while os.path.isfile(os.path.join(pca_dir, "pc.%i.dat" % i)):
+        rows = np.loadtxt(os.path.join(pca_dir, "pc.%i.dat" % i), ndmin=2)
+        mat = np.zeros((lay.xres, lay.yres))
+        ri, rj = rows[:, 0].astype(np.int64) - lay.xterm, rows[:, 1].astype(np.int64) - lay.yterm
+        ok = (ri >= 0) & (ri < lay.xres) & (rj >= 0) & (rj < lay.yres)
+        mat[ri[ok], rj[ok]] = rows[ok, 2]
+        coeff = mat[pi[sel] - lay.xterm, pj[sel] - lay.yterm]
+        print("Norm of PC # %i = %12.6f" % (i, math.sqrt(float((coeff ** 2).sum()))))
+        cols.append(coeff)
+        i += 1
+    n = i - 1
+    print("Reading in PC's.")
+    print("I found %i principal components..." % n)
+    if n == 0:
+        return None
+    sums = stage3.linregress_all(ctx.d_stack, ctx.P, ctx.nlevels, ctx.lut, ctx.time_vec[None], ctx.shift)
+    v = torch.from_numpy(np.stack(cols, axis=1)).to(ctx.d_stack.device)
+    return _project_pc(ctx, sel, sums["mean"][sel], v, change_sign=False)
+
+
 def pca(ctx, npc):
     """pca/pca_output.txt, pc.N.dat, pca_projections.dat (conan.py:1973-2001, :413-452)."""
     import torch
-    from scipy.stats import linregress
     os.makedirs("pca", exist_ok=True)
     sel = ctx.seen.astype(np.int32)
     print("There are a total of %i non-constant pairs." % len(sel))
@@ -162,28 +224,7 @@ def pca(ctx, npc):
     print("Diagonalizing....")
     w, v = stage3.top_eigenpairs(cov, npc)
     w = w.cpu().numpy()
-    # projections on the float16 mean-free vectors, as project_pc builds them (:430-450, :1981)
-    dev = ctx.d_stack.device
-    d_sel = torch.from_numpy(sel.astype(np.int64)).to(dev)
-    mean16 = torch.from_numpy(mean.astype(np.float32).astype(np.float16)).to(dev)
-    lut16 = ctx.lut.to(torch.float16)
-    proj = torch.empty((ctx.nf, npc), dtype=torch.float64, device=dev)
-    step = max(1, int(2.0e8 // max(len(sel), 1)))
-    for f0 in range(0, ctx.nf, step):
-        lv = ctx.d_stack[f0:f0 + step].view(torch.int16).to(torch.int64) & 0xffff
-        vm0 = (lut16[lv.index_select(1, d_sel)] - mean16[None, :]).double()      # float16 arithmetic, then widened
-        proj[f0:f0 + step] = vm0 @ v
-    proj = proj.cpu().numpy()
-    v = v.cpu().numpy()
-    print("Projecting principal components...")
-    for i in range(npc):
-        if linregress(proj[:, i], ctx.time_vec).rvalue < 0:
-            v[:, i] = -v[:, i]
-            proj[:, i] *= -1
-    with open("pca/pca_projections.dat", "w") as f:
-        for n in range(ctx.nf):
-            f.write("%12i" % ctx.time_vec[n])
-            f.write((npc * " %12.6f") % tuple(proj[n]) + "\n")
+    v, proj = _project_pc(ctx, sel, mean, v, change_sign=True)
     with open("pca/pca_output.txt", "w") as f:
         f.write("# Total variance: %f\n" % sum_var)
         f.write("# i (eigvalue i) (running sum to i) (explained variance)\n")
@@ -345,6 +386,8 @@ def run_all(opts, ret, s2, trunc, trunc_inter, nres, nterm, asymm_data):
         print("Starting contact map-based cluster analysis...")
         print("")
         cluster_trajectory(context(), opts['ks_traj'], trunc, trunc_inter, bool(asymm_data))
-    for k in ('pca_dir', 'blocking', 'k_res_clusters'):
+    if opts.get('pca_dir') and not opts.get('pca_make'):
+        pca_read(context(), opts['pca_dir'])
+    for k in ('blocking', 'k_res_clusters'):
         if opts.get(k):
             print("The %s analysis is outside the accelerated path and not available in this build." % k.upper())

@@ -119,6 +119,7 @@ def run_case(name, full, times, trunc, nlevels, keywords, obs=None, extra_files=
                 f.write("%d %s\n" % (t, " ".join("%.6f" % v for v in row)))
         text += "PEARSON_OBS obs.dat\n"
     for fname, content in (extra_files or {}).items():
+        os.makedirs(os.path.dirname(os.path.join(work, fname)), exist_ok=True)
         with open(os.path.join(work, fname), "w") as f:
             f.write(content)
     g = ref_runner.run_reference(work, text)
@@ -127,7 +128,7 @@ def run_case(name, full, times, trunc, nlevels, keywords, obs=None, extra_files=
     if obs is not None:
         out["in/obs"] = obs
     for k, v in parse_tree(work).items():
-        if k.startswith("input/") or k == "ref.inp" or k == "obs.dat":
+        if k.startswith("input/") or k.startswith("oldpca/") or k == "ref.inp" or k == "obs.dat":
             continue
         out["file/" + k] = v
     out["ret/vectors"] = np.asarray(g["vectors"])
@@ -164,8 +165,23 @@ def main():
     if only in (None, "zoom"):
         run_case("zoom", full[:30], times[:30], 1.0, nl, "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nMATRICES no\nZOOM_LIST zoom.txt\n",
                  extra_files={"zoom.txt": "# pairs\n2 7\n9 3\n1 12\n"})
-        if only:
-            return
+    if only in (None, "pcaread"):
+        # PCA_READ: principal components written by the reference's own PCA_MAKE run (case_hyst), read back and projected
+        hyst = np.load(os.path.join(OUT, "case_hyst.npz"))
+        pcs = {}
+        for k in (1, 2, 3):
+            rows = hyst["file/pca/pc.%d.dat" % k]
+            text, last = [], None
+            for i, j, v in rows:
+                if last is not None and i != last:
+                    text.append("\n")
+                text.append("%5i %5i %12.6f\n" % (i, j, v))
+                last = i
+            pcs["oldpca/pc.%d.dat" % k] = "".join(text) + "\n"
+        run_case("pcaread", full, times, 1.0, nl,
+                 "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nMATRICES no\nPCA_READ oldpca\n", extra_files=pcs)
+    if only:
+        return
     # finer legend: 1001 levels, trunc 1.5 (dx = 0.0015, not a multiple of 1e-4)
     full2 = synthetic_levels(12, 30, 9, 1001, 0.5, 0.6)
     run_case("fine", full2, np.arange(30) * 500 + 1000, 1.5, 1001,

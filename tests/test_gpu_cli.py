@@ -295,3 +295,28 @@ def test_import_api_return_tuple(lib, tmp_path, case):
     order = [pairs_legend[p] for p in want_pairs]        # the reference lists pairs in order of first appearance
     assert np.array_equal(got[order], c["ret/vectors"])
     assert np.array_equal(vectors[order[0]], c["ret/vectors"][0]) and len(vectors) == len(want_pairs)
+
+
+def test_pca_read_projects_on_components_of_an_earlier_run(lib, tmp_path):
+    """PCA_READ (conan.py:1073-1095): the components come from the reference's own PCA_MAKE run on the same stack
+    (case_hyst), the expected projections from the reference's PCA_READ run (case_pcaread)."""
+    from conan_b200 import xpm
+    c = np.load(os.path.join(GOLDEN, "case_pcaread.npz"))
+    hyst = np.load(os.path.join(GOLDEN, "case_hyst.npz"))
+    os.makedirs(str(tmp_path / "oldpca"))
+    for k in (1, 2, 3):
+        text, last = [], None
+        for i, j, v in hyst["file/pca/pc.%d.dat" % k]:
+            if last is not None and i != last:
+                text.append("\n")
+            text.append("%5i %5i %12.6f\n" % (i, j, v))
+            last = i
+        (tmp_path / "oldpca" / ("pc.%d.dat" % k)).write_text("".join(text) + "\n")
+    with open(str(tmp_path / "dmf.xpm"), "w") as f:
+        xpm.write_xpm(f, c["in/levels_full"], c["in/times"], float(c["in/trunc"]), int(c["in/nlevels"]))
+    out = _run_cli(str(tmp_path), str(c["in/keywords"]))
+    assert "I found 3 principal components" in out and "Norm of PC # 1" in out
+    got = np.loadtxt(str(tmp_path / "pca" / "pca_projections.dat"))
+    want = c["file/pca/pca_projections.dat"]
+    assert got.shape == want.shape and np.array_equal(got[:, 0], want[:, 0])
+    assert np.abs(got[:, 1:] - want[:, 1:]).max() <= 2.0e-6
