@@ -16,6 +16,7 @@
 //   operand_frames_kernel rows = frames, K = selected pairs: centred on the mean frame (distances
 //                         are translation invariant) and scaled by 1/norm (the operand of the
 //                         frame-frame Gram matrix), plus the squared row norms.
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -175,17 +176,18 @@ __global__ void residue_weights_kernel(const uint16_t* __restrict__ levels, int6
     for (int i = threadIdx.x; i < nout; i += blockDim.x) out[(size_t)blockIdx.x * nout + i] = s_w[i];
 }
 
-__device__ __forceinline__ float to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return __uint_as_float(r);
+// x = hi + lo with both parts binary16: hi carries the leading 11 significant bits, lo the next 11 (the caller
+// scales the operand so that |x| stays near 2^9 and neither part leaves the binary16 range where it matters).
+__device__ __forceinline__ void split_half(float x, __half& h, __half& l) {
+    h = __float2half_rn(x);
+    l = __float2half_rn(x - __half2float(h));
 }
 
 // rows = selected pairs, K = frames.  32 x 32 tiles through shared memory (a transpose of the stack).
 __global__ void operand_pairs_kernel(const uint16_t* __restrict__ levels, int64_t stride, int64_t nf,
                                      const int* __restrict__ sel, int nsel, const float* __restrict__ lut, int nlevels,
-                                     const float* __restrict__ mean, float* __restrict__ hi, float* __restrict__ lo,
-                                     int64_t ld /* elements per output row, multiple of 32 */) {
+                                     const float* __restrict__ mean, float scale, __half* __restrict__ hi,
+                                     __half* __restrict__ lo, int64_t ld /* elements per output row, multiple of 64 */) {
     __shared__ float tile[32][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8 threads
     const int64_t f0 = (int64_t)blockIdx.x * 32;
@@ -194,7 +196,7 @@ __global__ void operand_pairs_kernel(const uint16_t* __restrict__ levels, int64_
         const int64_t f = f0 + y;
         const int r = r0 + tx;
         float v = 0.f;
-        if (f < nf && r < nsel) v = lut[min((int)levels[f * stride + sel[r]], nlevels - 1)] - mean[r];
+        if (f < nf && r < nsel) v = (lut[min((int)levels[f * stride + sel[r]], nlevels - 1)] - mean[r]) * scale;
         tile[y][tx] = v;
     }
     __syncthreads();
@@ -203,9 +205,10 @@ __global__ void operand_pairs_kernel(const uint16_t* __restrict__ levels, int64_
         const int64_t f = f0 + tx;
         if (r < nsel && f < ld) {
             const float v = f < nf ? tile[tx][y] : 0.f;
-            const float h = to_tf32(v);
+            __half h, l;
+            split_half(v, h, l);
             hi[(size_t)r * ld + f] = h;
-            lo[(size_t)r * ld + f] = to_tf32(v - h);
+            lo[(size_t)r * ld + f] = l;
         }
     }
 }
@@ -213,18 +216,18 @@ __global__ void operand_pairs_kernel(const uint16_t* __restrict__ levels, int64_
 // rows = frames, K = selected pairs; also the squared norm of every row (float64).
 __global__ void operand_frames_kernel(const uint16_t* __restrict__ levels, int64_t stride, int64_t nf,
                                       const int* __restrict__ sel, int nsel, const float* __restrict__ lut, int nlevels,
-                                      const float* __restrict__ mean, float scale, float* __restrict__ hi,
-                                      float* __restrict__ lo, int64_t ld, double* __restrict__ norm2) {
+                                      const float* __restrict__ mean, float scale, __half* __restrict__ hi,
+                                      __half* __restrict__ lo, int64_t ld, double* __restrict__ norm2) {
     const int64_t f = blockIdx.x;
     double acc = 0.0;
     for (int64_t c = threadIdx.x; c < ld; c += blockDim.x) {
         float v = 0.f;
         if (c < nsel) v = (lut[min((int)levels[f * stride + sel[c]], nlevels - 1)] - mean[c]) * scale;
-        const float h = to_tf32(v);
-        const float l = to_tf32(v - h);
+        __half h, l;
+        split_half(v, h, l);
         hi[(size_t)f * ld + c] = h;
         lo[(size_t)f * ld + c] = l;
-        const double e = (double)h + (double)l;               // the value the GEMM effectively uses
+        const double e = (double)__half2float(h) + (double)__half2float(l);   // the value the GEMM effectively uses
         acc += e * e;
     }
     __shared__ double red[32];
@@ -289,24 +292,27 @@ extern "C" int conan_pearson_sums(const uint16_t* d_levels, int64_t levels_strid
 
 extern "C" int conan_build_operand(const uint16_t* d_levels, int64_t levels_stride, int64_t nf,
                                    const int32_t* d_sel, int32_t nsel, const float* d_lut, int32_t nlevels,
-                                   const float* d_mean, float scale, int32_t rows_are_frames, float* d_hi,
-                                   float* d_lo, int64_t ld, double* d_norm2, void* stream_) {
+                                   const float* d_mean, float scale, int32_t rows_are_frames, uint16_t* d_hi,
+                                   uint16_t* d_lo, int64_t ld, double* d_norm2, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (!d_levels || !d_sel || !d_lut || !d_mean || !d_hi || !d_lo)
         return conan::fail(CONAN_ERR_ARG, "conan_build_operand: null pointer argument");
     if (nf <= 0 || nsel <= 0 || nlevels < 2 || nlevels > kMaxLevels)
         return conan::fail(CONAN_ERR_ARG, "conan_build_operand: bad sizes");
     const int64_t k = rows_are_frames ? nsel : nf;
-    if (ld < k || ld % 32 != 0)
-        return conan::fail(CONAN_ERR_ARG, "conan_build_operand: ld=%lld must be a multiple of 32 and >= %lld", (long long)ld, (long long)k);
+    if (ld < k || ld % 64 != 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_build_operand: ld=%lld must be a multiple of 64 and >= %lld", (long long)ld, (long long)k);
+    if (!(scale > 0.f)) return conan::fail(CONAN_ERR_ARG, "conan_build_operand: scale must be positive");
+    __half* hi = reinterpret_cast<__half*>(d_hi);
+    __half* lo = reinterpret_cast<__half*>(d_lo);
     if (rows_are_frames) {
         if (!d_norm2) return conan::fail(CONAN_ERR_ARG, "conan_build_operand: frame rows need d_norm2");
         operand_frames_kernel<<<(unsigned)nf, 256, 0, stream>>>(d_levels, levels_stride, nf, d_sel, nsel, d_lut, nlevels,
-                                                               d_mean, scale, d_hi, d_lo, ld, d_norm2);
+                                                               d_mean, scale, hi, lo, ld, d_norm2);
     } else {
         dim3 grid((unsigned)(ld / 32), (unsigned)((nsel + 31) / 32));
         operand_pairs_kernel<<<grid, 256, 0, stream>>>(d_levels, levels_stride, nf, d_sel, nsel, d_lut, nlevels, d_mean,
-                                                       d_hi, d_lo, ld);
+                                                       scale, hi, lo, ld);
     }
     CONAN_CUDA_TRY(cudaGetLastError());
     return CONAN_OK;

@@ -1,17 +1,19 @@
-// Stage 3 on sm_100a: C = A * B^T in 3xTF32 on the 5th-generation tensor cores (tcgen05 / TMEM).
+// Stage 3 on sm_100a: C = A * B^T from three split products on the 5th-generation tensor cores (tcgen05 / TMEM).
 //
 // Serves the three dense contractions of the reference: the PCA covariance np.cov(vectors)
 // (conan.py:1983; A = B = centred pair series, K = frames), the frame-frame contact-map distances
 // scipy pdist(vectors.T / norm) (conan.py:2063; A = B = centred, scaled frame vectors, K = pairs,
 // epilogue sqrt(|a|^2 + |b|^2 - 2ab)), and pair-pair correlation blocks.
 //
-// Operands arrive already split into TF32 "hi" and "lo" parts (conan_build_operand): x = hi + lo
-// with both parts exactly representable in TF32, so hi*hi + hi*lo + lo*hi recovers float32-level
-// accuracy from three tensor-core products accumulated in float32 in TMEM.
+// Operands arrive split into a "hi" and a "lo" part (conan_build_operand): x = hi + lo, each part a
+// binary16 number -- the same 11-bit significands a TF32 split would give, in half the bytes -- so
+// hi*hi + hi*lo + lo*hi recovers float32-level accuracy from three tensor-core products accumulated in
+// float32 in TMEM ("3xTF32" with the parts stored as binary16: the kernel is bound by how fast operand
+// tiles reach the SM, and the f16 MMA path also runs at twice the TF32 rate).
 //
-// One CTA computes one 128 x 128 output tile: warp 0 = TMA producer (four 128-row x 32-float boxes
+// One CTA computes one 128 x 128 output tile: warp 0 = TMA producer (four 128-row x 64-element boxes
 // per k-block, 128-byte swizzle), warp 1 = TMEM allocator and single-thread tcgen05.mma issuer
-// (UMMA 128x128x8, twelve per k-block), warps 2-5 = epilogue (tcgen05.ld 32 lanes x 32 columns,
+// (UMMA 128x128x16, twelve per k-block), warps 2-5 = epilogue (tcgen05.ld 32 lanes x 32 columns,
 // scaling / distance epilogue, 128-bit stores).  A three-stage shared-memory ring is handed back and
 // forth with mbarriers; tcgen05.commit releases a stage when the MMAs that read it have retired.
 // The tensor core adds into its float32 accumulator with truncation, which would let the error grow
@@ -29,14 +31,14 @@
 
 namespace {
 
-constexpr int kBM = 128, kBN = 128, kBK = 32;      // tile, floats
+constexpr int kBM = 128, kBN = 128, kBK = 64;      // tile; kBK binary16 elements = 128 bytes per row
 constexpr int kStages = 3;
-constexpr int kOperandBytes = kBM * kBK * 4;        // 16 KB: 128 rows x 128 B
+constexpr int kOperandBytes = kBM * kBK * 2;        // 16 KB: 128 rows x 128 B
 constexpr int kStageBytes = 4 * kOperandBytes;      // A_hi, A_lo, B_hi, B_lo
 constexpr int kThreads = 192;
 constexpr int kTmemCols = 256;                       // two 128-column accumulators, used alternately
-constexpr int kChunkKb = 4;                          // k-blocks accumulated inside the tensor core before a drain
-constexpr int kUmmaK = 8;                           // TF32: 32 bytes per MMA along K
+constexpr int kChunkKb = 2;                          // k-blocks accumulated inside the tensor core before a drain
+constexpr int kUmmaK = 16;                          // binary16: 32 bytes per MMA along K
 constexpr int kBand = 8;                            // tile rows per band of the launch order
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -78,14 +80,14 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
     d |= (uint64_t)2 << 61;                           // SWIZZLE_128B
     return d;
 }
-// kind::tf32, D = F32, A and B K-major, M = 128, N = 128.
-constexpr uint32_t kInstrDesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+// kind::f16: D = F32 (bits 4-5 = 1), A and B binary16 (format fields 0), both K-major, M = 128, N = 128.
+constexpr uint32_t kInstrDesc = (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
 
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(kInstrDesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -105,10 +107,10 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 }
 
 struct GemmParams {
-    int M, N, K;                // K a multiple of 32 (operands are zero padded)
+    int M, N, K;                // K a multiple of 64 (operands are zero padded)
     float* C;
     int64_t ldc;
-    int epilogue;               // 0: alpha * acc   1: sqrt(max(0, rn[m] + cn[n] - 2 acc))
+    int epilogue;               // 0: alpha * acc   1: alpha * sqrt(max(0, rn[m] + cn[n] - 2 acc))
     float alpha;
     const double* row_norm2;    // epilogue 1
     const double* col_norm2;
@@ -190,10 +192,10 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__
                 const uint64_t dBh = make_smem_desc(base + 2 * kOperandBytes), dBl = make_smem_desc(base + 3 * kOperandBytes);
 #pragma unroll
                 for (int k = 0; k < kBK / kUmmaK; k++) {
-                    const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);   // 32 bytes per step, 16-byte units
-                    umma_tf32(acc, dAh + adv, dBh + adv, !(chunk_start && k == 0));
-                    umma_tf32(acc, dAh + adv, dBl + adv, 1);
-                    umma_tf32(acc, dAl + adv, dBh + adv, 1);
+                    const uint64_t adv = (uint64_t)((k * kUmmaK * 2) >> 4);   // 32 bytes per step, 16-byte units
+                    umma_f16(acc, dAh + adv, dBh + adv, !(chunk_start && k == 0));
+                    umma_f16(acc, dAh + adv, dBl + adv, 1);
+                    umma_f16(acc, dAl + adv, dBh + adv, 1);
                 }
                 umma_commit(&empty_bar[s]);          // the stage may be refilled once these MMAs retire
                 if ((kb % kChunkKb) == kChunkKb - 1 || kb == nkb - 1)
@@ -234,7 +236,7 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__
                 const float acc = racc[c * 32 + j];
                 if (prm.epilogue == 1) {
                     const float cn = (nb + j < prm.N) ? (float)prm.col_norm2[nb + j] : 0.f;
-                    o[j] = sqrtf(fmaxf(rn + cn - 2.f * acc, 0.f));
+                    o[j] = prm.alpha * sqrtf(fmaxf(rn + cn - 2.f * acc, 0.f));
                 } else {
                     o[j] = prm.alpha * acc;
                 }
@@ -279,12 +281,12 @@ EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-int make_map(EncodeTiledFn enc, CUtensorMap* map, const float* base, int rows, int64_t ld) {
+int make_map(EncodeTiledFn enc, CUtensorMap* map, const uint16_t* base, int rows, int64_t ld) {
     cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)rows};
-    cuuint64_t gstr[1] = {(cuuint64_t)ld * 4};
+    cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
     cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)kBM};
     cuuint32_t estr[2] = {1, 1};
-    CUresult cr = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
+    CUresult cr = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<uint16_t*>(base), gdim, gstr, box, estr,
                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return cr == CUDA_SUCCESS ? 0 : (int)cr;
@@ -292,16 +294,16 @@ int make_map(EncodeTiledFn enc, CUtensorMap* map, const float* base, int rows, i
 
 }  // namespace
 
-extern "C" int conan_gemm_3xtf32(const float* d_a_hi, const float* d_a_lo, int32_t M, const float* d_b_hi,
-                                 const float* d_b_lo, int32_t N, int64_t K, int64_t ld, int32_t epilogue, float alpha,
+extern "C" int conan_gemm_3xtf32(const uint16_t* d_a_hi, const uint16_t* d_a_lo, int32_t M, const uint16_t* d_b_hi,
+                                 const uint16_t* d_b_lo, int32_t N, int64_t K, int64_t ld, int32_t epilogue, float alpha,
                                  const double* d_row_norm2, const double* d_col_norm2, int32_t symmetric, float* d_c,
                                  int64_t ldc, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (!d_a_hi || !d_a_lo || !d_b_hi || !d_b_lo || !d_c)
         return conan::fail(CONAN_ERR_ARG, "conan_gemm_3xtf32: null pointer argument");
-    if (M <= 0 || N <= 0 || K <= 0 || ld < K || ld % 32 != 0 || ldc < N)
+    if (M <= 0 || N <= 0 || K <= 0 || ld < K || ld % 64 != 0 || ldc < N)
         return conan::fail(CONAN_ERR_ARG, "conan_gemm_3xtf32: bad sizes M=%d N=%d K=%lld ld=%lld ldc=%lld (ld must be a "
-                           "multiple of 32 and >= K)", M, N, (long long)K, (long long)ld, (long long)ldc);
+                           "multiple of 64 and >= K)", M, N, (long long)K, (long long)ld, (long long)ldc);
     if (epilogue == 1 && (!d_row_norm2 || !d_col_norm2))
         return conan::fail(CONAN_ERR_ARG, "conan_gemm_3xtf32: the distance epilogue needs both norm arrays");
     if (epilogue != 0 && epilogue != 1) return conan::fail(CONAN_ERR_ARG, "conan_gemm_3xtf32: unknown epilogue %d", epilogue);

@@ -111,8 +111,8 @@ def covariance_sharded(levels, sel, nlevels, d_lut, mean, nf_total, group=None):
     dev = levels.device
     d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
     d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
-    hi, lo, _ = stage3.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=False)
-    cov = stage3.gemm_3xtf32(hi, lo, hi, lo, levels.shape[0], epilogue=0, alpha=1.0 / (nf_total - 1), symmetric=True)
+    hi, lo, _, s = stage3.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=False)
+    cov = stage3.gemm_3xtf32(hi, lo, hi, lo, levels.shape[0], epilogue=0, alpha=1.0 / ((nf_total - 1) * s * s), symmetric=True)
     dist.all_reduce(cov, op=dist.ReduceOp.SUM, group=group)
     return cov
 
@@ -127,14 +127,14 @@ def frame_distances_sharded(levels, sel, nlevels, d_lut, mean, norm, group=None)
     dev = levels.device
     d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
     d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
-    hi, lo, n2 = stage3.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
+    hi, lo, n2, s = stage3.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
     counts = torch.zeros(world, dtype=torch.int64, device=dev)
     counts[rank] = levels.shape[0]
     dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
     counts = [int(c) for c in counts.cpu()]
     total, ld = sum(counts), hi.shape[1]
-    all_hi = torch.empty((total, ld), dtype=torch.float32, device=dev)
-    all_lo = torch.empty((total, ld), dtype=torch.float32, device=dev)
+    all_hi = torch.empty((total, ld), dtype=torch.float16, device=dev)
+    all_lo = torch.empty((total, ld), dtype=torch.float16, device=dev)
     all_n2 = torch.empty(total, dtype=torch.float64, device=dev)
     o = 0
     for r in range(world):
@@ -145,5 +145,6 @@ def frame_distances_sharded(levels, sel, nlevels, d_lut, mean, norm, group=None)
                 part.copy_(mine)
             dist.broadcast(part, src=src, group=group)
         o += counts[r]
-    block = stage3.gemm_3xtf32(hi, lo, all_hi, all_lo, len(sel), epilogue=1, row_norm2=n2, col_norm2=all_n2, symmetric=False)
+    block = stage3.gemm_3xtf32(hi, lo, all_hi, all_lo, len(sel), epilogue=1, alpha=1.0 / s, row_norm2=n2, col_norm2=all_n2,
+                               symmetric=False)
     return block, sum(counts[:rank])

@@ -5,6 +5,8 @@ Stand where the reference calls scipy.stats.linregress per pair (conan.py:1888-1
 the stack through a table (lut16), the contractions run in conan_pearson_sums (streaming) and
 conan_gemm_3xtf32 (tcgen05 tensor cores).
 """
+import math
+
 import numpy as np
 import torch
 
@@ -102,27 +104,38 @@ def linregress_all(d_stack, P, nlevels, d_lut, xs, shift, frame_mask=None):
     return out
 
 
+def operand_scale(d_lut, scale=1.0):
+    """Power of two that brings |centred value * scale| near 2^9 (centred values lie within +- the largest
+    distance of the legend): the two binary16 parts of the split then sit well inside the half range."""
+    bound = float(d_lut.float().max().item()) * float(scale)
+    return 2.0 ** math.floor(math.log2(512.0 / max(bound, 1.0e-30)))
+
+
 def build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames, scale=1.0):
-    """(hi, lo, norm2) device tensors: centred operand split for 3xTF32; rows = pairs or frames."""
+    """(hi, lo, norm2, s) for conan_gemm_3xtf32: the centred operand times scale * s, split into two binary16
+    parts (rows = pairs or frames); s is the power of two from operand_scale, norm2 the squared norms of the
+    scaled rows (frame rows only)."""
     lib = _lib.load()
     dev = d_stack.device
     nf, stride = d_stack.shape
     nsel = d_sel.numel()
     rows, k = (nf, nsel) if rows_are_frames else (nsel, nf)
-    ld = (k + 31) // 32 * 32
-    hi = torch.empty((rows, ld), dtype=torch.float32, device=dev)
-    lo = torch.empty((rows, ld), dtype=torch.float32, device=dev)
+    ld = (k + 63) // 64 * 64
+    s = operand_scale(d_lut, scale)
+    hi = torch.empty((rows, ld), dtype=torch.float16, device=dev)
+    lo = torch.empty((rows, ld), dtype=torch.float16, device=dev)
     norm2 = torch.empty(rows, dtype=torch.float64, device=dev) if rows_are_frames else None
     _lib.check(lib.conan_build_operand(d_stack.data_ptr(), stride, nf, d_sel.data_ptr(), nsel, d_lut.data_ptr(), nlevels,
-                                       d_mean.data_ptr(), float(scale), 1 if rows_are_frames else 0, hi.data_ptr(),
+                                       d_mean.data_ptr(), float(scale) * s, 1 if rows_are_frames else 0, hi.data_ptr(),
                                        lo.data_ptr(), ld, 0 if norm2 is None else norm2.data_ptr(), _stream(dev)))
-    return hi, lo, norm2
+    return hi, lo, norm2, s
 
 
 def gemm_3xtf32(a_hi, a_lo, b_hi, b_lo, K, epilogue=0, alpha=1.0, row_norm2=None, col_norm2=None, symmetric=False, out=None):
-    """C = epilogue(A B^T) on the tensor cores; operands [rows, ld] float32 hi / lo parts."""
+    """C = epilogue(A B^T) on the tensor cores; operands [rows, ld] binary16 hi / lo parts."""
     lib = _lib.load()
     dev = a_hi.device
+    assert a_hi.dtype == torch.float16 and b_hi.dtype == torch.float16
     M, ld = a_hi.shape
     N = b_hi.shape[0]
     if out is None:
@@ -140,8 +153,8 @@ def covariance(d_stack, sel, nlevels, d_lut, mean):
     nf = d_stack.shape[0]
     d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
     d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
-    hi, lo, _ = build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames=False)
-    return gemm_3xtf32(hi, lo, hi, lo, nf, epilogue=0, alpha=1.0 / (nf - 1), symmetric=True)
+    hi, lo, _, s = build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames=False)
+    return gemm_3xtf32(hi, lo, hi, lo, nf, epilogue=0, alpha=1.0 / ((nf - 1) * s * s), symmetric=True)
 
 
 def frame_distances(d_stack, sel, nlevels, d_lut, mean, norm):
@@ -149,8 +162,8 @@ def frame_distances(d_stack, sel, nlevels, d_lut, mean, norm):
     dev = d_stack.device
     d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
     d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
-    hi, lo, n2 = build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
-    return gemm_3xtf32(hi, lo, hi, lo, len(sel), epilogue=1, row_norm2=n2, col_norm2=n2, symmetric=True)
+    hi, lo, n2, s = build_operand(d_stack, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
+    return gemm_3xtf32(hi, lo, hi, lo, len(sel), epilogue=1, alpha=1.0 / s, row_norm2=n2, col_norm2=n2, symmetric=True)
 
 
 def top_eigenpairs(cov, k, tol=1.0e-11, block_extra=6, depth=8, max_cycles=40, dense_below=2048):

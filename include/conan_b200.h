@@ -254,25 +254,32 @@ int conan_level_range(const uint16_t* d_levels, int64_t levels_stride, int64_t n
 int conan_residue_weights(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int32_t symmetric,
                           int32_t xres, int32_t yres, int32_t nlevels, int32_t* d_out, void* stream);
 
-/* Builds a GEMM operand from the stack, centred and split into TF32 hi / lo parts (x = hi + lo).
+/* Builds a GEMM operand from the stack, centred, scaled and split into hi / lo parts (x = hi + lo).
  * rows_are_frames = 0: rows = the nsel selected pairs d_sel (indices into the P columns), K = frames,
- *     x = y - d_mean[row]                       -- the operand of np.cov(vectors), conan.py:1983.
+ *     x = (y - d_mean[row]) * scale             -- the operand of np.cov(vectors), conan.py:1983.
  * rows_are_frames = 1: rows = frames, K = selected pairs, x = (y - d_mean[col]) * scale, and
  *     d_norm2[row] = |x|^2 (float64)            -- the operand of pdist(vectors.T / norm), conan.py:2063
  *     (centring on the mean frame leaves distances unchanged and keeps the Gram form accurate).
- * d_hi / d_lo are [rows][ld] float32, ld a multiple of 32 >= K; the padding is written as zeros. */
+ * scale multiplies every centred value (1/norm of conan.py:2038-2041 for frame rows, times a power of
+ * two chosen by the caller so that |value * scale| stays near 2^9: both parts of the split are binary16).
+ * d_hi / d_lo are [rows][ld] binary16 (hi = half(x), lo = half(x - hi)), ld a multiple of 64 >= K;
+ * the padding is written as zeros.  d_norm2 is the squared norm of the scaled rows. */
 int conan_build_operand(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, const int32_t* d_sel,
                         int32_t nsel, const float* d_lut, int32_t nlevels, const float* d_mean, float scale,
-                        int32_t rows_are_frames, float* d_hi, float* d_lo, int64_t ld, double* d_norm2,
+                        int32_t rows_are_frames, uint16_t* d_hi, uint16_t* d_lo, int64_t ld, double* d_norm2,
                         void* stream);
 
-/* C [M][N] (float32, row pitch ldc) = epilogue(A * B^T), A = a_hi + a_lo [M][ld], B = b_hi + b_lo [N][ld],
- * as hi*hi + hi*lo + lo*hi on the tcgen05 tensor cores (3xTF32), float32 accumulation in TMEM.
- * epilogue 0: alpha * acc                      (covariance: alpha = 1/(nf-1), conan.py:1983)
- * epilogue 1: sqrt(max(0, row_norm2[m] + col_norm2[n] - 2 acc))   (frame-frame distance, conan.py:2063)
+/* C [M][N] (float32, row pitch ldc) = epilogue(A * B^T), A = a_hi + a_lo [M][ld], B = b_hi + b_lo [N][ld]
+ * (binary16 parts), as hi*hi + hi*lo + lo*hi on the tcgen05 tensor cores: the three-product split known as
+ * 3xTF32 -- the parts carry the same 11-bit significands -- stored as binary16 and issued as kind::f16 MMAs,
+ * float32 accumulation in TMEM.
+ * epilogue 0: alpha * acc                      (covariance: alpha = 1/((nf-1) s^2), conan.py:1983; s = the
+ *                                               operand's power-of-two scale)
+ * epilogue 1: alpha * sqrt(max(0, row_norm2[m] + col_norm2[n] - 2 acc))   (frame-frame distance,
+ *                                               conan.py:2063; alpha = 1/s)
  * symmetric != 0 (needs A == B): only the upper triangle of 128 x 128 tiles is computed, both halves written. */
-int conan_gemm_3xtf32(const float* d_a_hi, const float* d_a_lo, int32_t M, const float* d_b_hi,
-                      const float* d_b_lo, int32_t N, int64_t K, int64_t ld, int32_t epilogue, float alpha,
+int conan_gemm_3xtf32(const uint16_t* d_a_hi, const uint16_t* d_a_lo, int32_t M, const uint16_t* d_b_hi,
+                      const uint16_t* d_b_lo, int32_t N, int64_t K, int64_t ld, int32_t epilogue, float alpha,
                       const double* d_row_norm2, const double* d_col_norm2, int32_t symmetric, float* d_c,
                       int64_t ldc, void* stream);
 

@@ -113,17 +113,17 @@ def test_gemm_general_rectangular(lib):
     M, N, K = 200, 333, 70
     a, b = rng.normal(size=(M, K)), rng.normal(size=(N, K))
 
-    def split(x):
-        ld = (x.shape[1] + 31) // 32 * 32
+    def split(x, scale=64.0):
+        ld = (x.shape[1] + 63) // 64 * 64
         t = torch.zeros((x.shape[0], ld), dtype=torch.float32)
-        t[:, :x.shape[1]] = torch.from_numpy(x.astype(np.float32))
-        hi = (t.view(torch.int32) + 0x1000 & ~0x1fff).view(torch.float32)     # round to TF32 (10-bit mantissa)
-        lo = ((t - hi).view(torch.int32) + 0x1000 & ~0x1fff).view(torch.float32)
+        t[:, :x.shape[1]] = torch.from_numpy(x.astype(np.float32)) * scale
+        hi = t.to(torch.float16)
+        lo = (t - hi.float()).to(torch.float16)
         return hi.cuda(), lo.cuda()
 
     ah, al = split(a)
     bh, bl = split(b)
-    got = stage3.gemm_3xtf32(ah, al, bh, bl, K, alpha=0.5).cpu().numpy()
+    got = stage3.gemm_3xtf32(ah, al, bh, bl, K, alpha=0.5 / (64.0 * 64.0)).cpu().numpy()
     want = 0.5 * a.astype(np.float32).astype(np.float64) @ b.astype(np.float32).astype(np.float64).T
     assert _frob(got, want) < 2e-6, _frob(got, want)
 
