@@ -87,13 +87,14 @@ def pair_stats_sharded(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0, 
 # ------------------------------------------------------------------------------------------------
 # stage 3 on frame shards ("GEMMs")
 # ------------------------------------------------------------------------------------------------
-def global_mean(levels, P, nlevels, d_lut, shift, group=None):
+def global_mean(levels, P, nlevels, d_lut, shift, group=None, ops=None):
     """Mean float16 distance of every pair over ALL ranks' frames (float64 [P] on the host): the local sums of
     (value - shift) are added across ranks.  `shift` must be the same on every rank (e.g. from the merged sum_k)."""
     import numpy as np
-    from . import stage3
+    if ops is None:
+        from . import stage3 as ops          # (the CPU tests pass stand-ins for the kernels)
     nf = levels.shape[0]
-    local = stage3.linregress_all(levels, P, nlevels, d_lut, np.zeros((1, nf)), shift)["mean"]     # local mean, float64
+    local = ops.linregress_all(levels, P, nlevels, d_lut, np.zeros((1, nf)), shift)["mean"]     # local mean, float64
     shift_h = shift.cpu().numpy() if torch.is_tensor(shift) else np.asarray(shift)
     t = torch.from_numpy((local - shift_h.astype(np.float64)) * nf).to(levels.device)
     n = torch.tensor([float(nf)], dtype=torch.float64, device=levels.device)
@@ -102,39 +103,41 @@ def global_mean(levels, P, nlevels, d_lut, shift, group=None):
     return shift_h.astype(np.float64) + t.cpu().numpy() / float(n.item()), int(round(float(n.item())))
 
 
-def covariance_sharded(levels, sel, nlevels, d_lut, mean, nf_total, group=None):
+def covariance_sharded(levels, sel, nlevels, d_lut, mean, nf_total, group=None, ops=None):
     """np.cov(vectors) over all ranks' frames: the frame axis is the contraction axis, so every rank contracts its
     own frames with the global means (3xTF32 tensor-core GEMM) and the [nsel, nsel] partial products are summed
     with one all-reduce.  Every rank returns the full matrix."""
     import numpy as np
-    from . import stage3
+    if ops is None:
+        from . import stage3 as ops
     dev = levels.device
     d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
     d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
-    hi, lo, _, s = stage3.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=False)
-    cov = stage3.gemm_3xtf32(hi, lo, hi, lo, levels.shape[0], epilogue=0, alpha=1.0 / ((nf_total - 1) * s * s), symmetric=True)
+    hi, lo, _, s = ops.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=False)
+    cov = ops.gemm_3xtf32(hi, lo, hi, lo, levels.shape[0], epilogue=0, alpha=1.0 / ((nf_total - 1) * s * s), symmetric=True)
     dist.all_reduce(cov, op=dist.ReduceOp.SUM, group=group)
     return cov
 
 
-def frame_distances_sharded(levels, sel, nlevels, d_lut, mean, norm, group=None):
+def frame_distances_sharded(levels, sel, nlevels, d_lut, mean, norm, group=None, ops=None):
     """Rows [this rank's frames] x [all frames] of pdist(vectors.T / norm): the output is partitioned by frame
     rows, the centred operands of the other ranks' frames arrive by broadcast (NVLink), and each rank runs the
     distance-epilogue GEMM for its row block.  Returns (block [nf_local, nf_total] float32, frame offset)."""
     import numpy as np
-    from . import stage3
+    if ops is None:
+        from . import stage3 as ops
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     dev = levels.device
     d_sel = torch.from_numpy(np.ascontiguousarray(sel, np.int32)).to(dev)
     d_mean = torch.from_numpy(np.ascontiguousarray(mean, np.float32)).to(dev)
-    hi, lo, n2, s = stage3.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
+    hi, lo, n2, s = ops.build_operand(levels, d_sel, nlevels, d_lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
     counts = torch.zeros(world, dtype=torch.int64, device=dev)
     counts[rank] = levels.shape[0]
     dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
     counts = [int(c) for c in counts.cpu()]
     total, ld = sum(counts), hi.shape[1]
-    all_hi = torch.empty((total, ld), dtype=torch.float16, device=dev)
-    all_lo = torch.empty((total, ld), dtype=torch.float16, device=dev)
+    all_hi = torch.empty((total, ld), dtype=hi.dtype, device=dev)
+    all_lo = torch.empty((total, ld), dtype=lo.dtype, device=dev)
     all_n2 = torch.empty(total, dtype=torch.float64, device=dev)
     o = 0
     for r in range(world):
@@ -145,6 +148,6 @@ def frame_distances_sharded(levels, sel, nlevels, d_lut, mean, norm, group=None)
                 part.copy_(mine)
             dist.broadcast(part, src=src, group=group)
         o += counts[r]
-    block = stage3.gemm_3xtf32(hi, lo, all_hi, all_lo, len(sel), epilogue=1, alpha=1.0 / s, row_norm2=n2, col_norm2=all_n2,
+    block = ops.gemm_3xtf32(hi, lo, all_hi, all_lo, len(sel), epilogue=1, alpha=1.0 / s, row_norm2=n2, col_norm2=all_n2,
                                symmetric=False)
     return block, sum(counts[:rank])
