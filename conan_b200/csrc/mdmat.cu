@@ -192,6 +192,10 @@ __device__ __forceinline__ float min_image(float d, float L) {
     return d;
 }
 
+__device__ __forceinline__ float nearest_image(float d, float L) {
+    return L > 0.f ? fmaf(-rintf(__fdividef(d, L)), L, d) : d;
+}
+
 // r2 exactly as the CPU restatement computes it: every operation rounded, no contraction.
 __device__ __forceinline__ float dist2_exact(float dx, float dy, float dz) {
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
@@ -336,13 +340,21 @@ __device__ __forceinline__ int fast_pair(const MdmatParams& prm, const float* __
                                          const float* __restrict__ aJp, int pstride, float4 si, float4 sj,
                                          int ci, int cj, const float* __restrict__ box) {
     float Dx = sj.x - si.x, Dy = sj.y - si.y, Dz = sj.z - si.z;
-    if (PBC) { Dx = min_image(Dx, box[0]); Dy = min_image(Dy, box[4]); Dz = min_image(Dz, box[8]); }
+    // box = the three box lengths of the frame.  Only pairs whose spheres stay inside half a box come here, so
+    // the centre difference is well clear of +-L/2 and the nearest-image shift can be taken by rounding.
+    bool shifted = false;
+    if (PBC) {
+        const float Rx = Dx, Ry = Dy, Rz = Dz;
+        Dx = nearest_image(Dx, box[0]); Dy = nearest_image(Dy, box[1]); Dz = nearest_image(Dz, box[2]);
+        shifted = Dx != Rx || Dy != Ry || Dz != Rz;
+    }
     const float rr = si.w + sj.w;
     const float D2 = fmaf(Dz, Dz, fmaf(Dy, Dy, Dx * Dx));
     // |computed - reference r2| <= 22 u (rr + |D|)^2 <= 44 u (rr^2 + D2); 64 u leaves margin.
     float E = kErrC * fmaf(rr, rr, D2);
-    // the reference forms a - b before shifting by a box length: an extra u * L per component
-    if (PBC) E += 2.5e-7f * fmaxf(box[0], fmaxf(box[4], box[8])) * (rr + sqrtf(D2));
+    // a pair that is brought together by a lattice shift: the reference forms a - b (of the size of the box)
+    // before shifting, and so does the centre difference here: an extra u * L per component
+    if (PBC && shifted) E += 2.5e-7f * fmaxf(box[0], fmaxf(box[1], box[2])) * (rr + D2 * rsqrtf(fmaxf(D2, 1.0e-12f)) * 1.001f);
     float m = 3.0e38f;
     int a0 = 0;
     while (ci - a0 > 4) { m = chunk_min_fast<8>(aIp, aJp, pstride, a0, cj, Dx, Dy, Dz, m); a0 += 8; }
@@ -381,6 +393,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     int* rowbase = counters + 6;                        // [64] element index of pair (row residue, residue 0) in a frame row
     int* origI = rowbase + kTile;                       // [64] residue at row position i / column position j of the tile
     int* origJ = origI + kTile;
+    float* boxs = reinterpret_cast<float*>(origJ + kTile);   // [kMaxFB][3] box lengths of the group's frames (periodic runs)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t blk = blockIdx.x;
@@ -441,8 +454,14 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             }
         }
     }
-    // per-frame spheres, and for the plain (non-periodic) case one sphere per residue that holds it
-    // in every frame of the group, so the pruning runs once per group instead of once per frame
+    // per-frame spheres, and one sphere per residue that holds it in every frame of the group, so the
+    // pruning runs once per group instead of once per frame.  In a periodic run the residue's centre in
+    // frame g is its centre in the group's first frame plus the minimum image of the displacement, modulo
+    // that frame's box, which is all the torus triangle inequality of the pruning test needs.
+    if (PBC && tid >= 2 * kTile && tid < 2 * kTile + nfb * 3) {
+        const int q = tid - 2 * kTile;
+        boxs[q] = prm.box[9 * (f0 + q / 3) + 4 * (q % 3)];
+    }
     if (tid < 2 * kTile) {
         const bool isI = tid < kTile;
         const int l = isI ? tid : tid - kTile;
@@ -455,7 +474,11 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         for (int g = 1; g < nfb; g++) {
             const float4 sg = src[(size_t)g * prm.nres_pad];
             dst[g * kTile + l] = sg;
-            const float dx = sg.x - s0.x, dy = sg.y - s0.y, dz = sg.z - s0.z;
+            float dx = sg.x - s0.x, dy = sg.y - s0.y, dz = sg.z - s0.z;
+            if (PBC) {
+                const float* b = prm.box + 9 * (f0 + g);
+                dx = min_image(dx, b[0]); dy = min_image(dy, b[4]); dz = min_image(dz, b[8]);
+            }
             R = fmaxf(R, sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx))) * 1.000001f + sg.w);
         }
         (isI ? grpI : grpJ)[l] = make_float4(s0.x, s0.y, s0.z, R);
@@ -496,22 +519,19 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     bool tiles_ready = !prm.use_tma;
 
     // ---- survivors: fast expanded form, exact redo where the level is not certain ----------
-    // The list holds residue pairs; without periodicity an entry stands for the pair in every frame
-    // of the group (items = entries x frames), with periodicity entries carry their frame.
+    // The list holds residue pairs; an entry stands for the pair in every frame of the group
+    // (items = entries x frames).
     auto process_list = [&]() {
         if (!tiles_ready) { mbar_wait(bar, 0); tiles_ready = true; }
         const int nent = counters[0];
-        const int nitems = PBC ? nent : nent * nfb;
+        const int nitems = nent * nfb;
         int near = 0, evals = 0;
         int gq = 0, qq = tid;      // frame-major walk over (frame, entry): a warp's lanes share the frame,
                                    // so their tile reads fall into different banks
         for (int s = tid; s < nitems; s += kThreads, qq += kThreads) {
             int e, g;
-            if (PBC) { e = list[s]; g = e >> 13; }
-            else {
-                while (qq >= nent) { qq -= nent; gq++; }
-                g = gq; e = list[qq];
-            }
+            while (qq >= nent) { qq -= nent; gq++; }
+            g = gq; e = list[qq];
             const int i = e & 63, j = (e >> 6) & 63;
             const int ci = cntI[i], cj = cntJ[j];
             evals += ci * cj;
@@ -519,7 +539,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             if (!PBC || !(e & 0x1000))
                 level = fast_pair<PBC>(prm, aI + (size_t)g * kPlanesI * pstride + i, aJ + (size_t)g * kPlanesJ * pstride + j,
                                        pstride, sphI[g * kTile + i], sphJ[g * kTile + j], ci, cj,
-                                       PBC ? prm.box + 9 * (f0 + g) : nullptr);
+                                       PBC ? boxs + 3 * g : nullptr);
             if (level < 0) {
                 const int k = atom_add_shared(&counters[1], 1);
                 if (k < kSlowCap) {
@@ -561,15 +581,18 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
 
     // ---- bounding-sphere pruning, survivors compacted into the list -------------------------
     const float half_trunc = 0.5f * prm.trunc;
-    const int npass = PBC ? nfb : 1;
-    for (int g = 0; g < npass; g++) {
-        if (PBC && counters[0] > kListCap - kTile * kTile) process_list();   // uniform: the count is stable here
-        const float4* sI = PBC ? sphI + g * kTile : grpI;
-        const float4* sJ = PBC ? sphJ + g * kTile : grpJ;
+    {
+        const float4* sI = grpI;
+        const float4* sJ = grpJ;
+        // periodic runs: the smallest box of the group (for the half-box test) and whether all boxes are equal
         float Lx = 0.f, Ly = 0.f, Lz = 0.f;
+        bool same_box = true;
         if (PBC) {
-            const float* b = prm.box + 9 * (f0 + g);
-            Lx = b[0]; Ly = b[4]; Lz = b[8];
+            Lx = boxs[0]; Ly = boxs[1]; Lz = boxs[2];
+            for (int q = 1; q < nfb; q++) {
+                same_box = same_box && boxs[3 * q] == boxs[0] && boxs[3 * q + 1] == boxs[1] && boxs[3 * q + 2] == boxs[2];
+                Lx = fminf(Lx, boxs[3 * q]); Ly = fminf(Ly, boxs[3 * q + 1]); Lz = fminf(Lz, boxs[3 * q + 2]);
+            }
         }
         // The tile is taken in 16 x 16 sub-blocks, two per warp.  Rows and columns are sorted by residue
         // size (block_perm_kernel), so the pairs of a sub-block have similar numbers of atoms on both
@@ -594,9 +617,21 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 float dx = si.x - sj.x, dy = si.y - sj.y, dz = si.z - sj.z;
                 bool general = false;
                 if (PBC) {
+                    // the distance of the group centres on the torus: per component the smallest minimum
+                    // image over the frames' boxes (one evaluation when the box does not change)
+                    if (same_box) {
+                        dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz);
+                    } else {
+                        float mx = 3.0e38f, my = 3.0e38f, mz = 3.0e38f;
+                        for (int q = 0; q < nfb; q++) {
+                            mx = fminf(mx, fabsf(min_image(dx, boxs[3 * q])));
+                            my = fminf(my, fabsf(min_image(dy, boxs[3 * q + 1])));
+                            mz = fminf(mz, fabsf(min_image(dz, boxs[3 * q + 2])));
+                        }
+                        dx = mx; dy = my; dz = mz;
+                    }
                     // one lattice shift serves every atom pair only if the spheres stay inside half a box
                     const float rr = si.w + sj.w;
-                    dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz);
                     general = !(fabsf(dx) + rr < 0.49999f * Lx && fabsf(dy) + rr < 0.49999f * Ly &&
                                 fabsf(dz) + rr < 0.49999f * Lz);
                 }
@@ -617,7 +652,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 for (int k = 0; k < 8; k++)
                     if ((keepbits >> k) & 1u) {
                         const int i = rb + (lane >> 4) + 2 * k;
-                        list[base + before[k]] = (uint16_t)(i | (j << 6) | (((genbits >> k) & 1u) ? 0x1000 : 0) | (PBC ? (g << 13) : 0));
+                        list[base + before[k]] = (uint16_t)(i | (j << 6) | (((genbits >> k) & 1u) ? 0x1000 : 0));
                     }
             }
         }
@@ -663,6 +698,7 @@ size_t mdmat_smem_bytes(int kpad, int fb) {
     s += 2 * kTile * sizeof(int);                               // counts
     s += (size_t)(kListCap + kSlowCap) * sizeof(uint16_t);      // survivor and redo lists
     s += 8 + 6 * sizeof(int) + 3 * kTile * sizeof(int);         // mbarrier + counters + row bases + residue numbers
+    s += kMaxFB * 3 * sizeof(float);                            // box lengths of the group's frames
     return (s + 15) & ~(size_t)15;
 }
 

@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(kDecodeThreads) xtc_decode_kernel(const Decode
         if (off + 56 + (int64_t)natoms * 12 > prm.nbytes) return finish(kBadHeader);
         for (int a = lane; a < natoms; a += 32) {
             const int s = slot ? slot[a] : a;
-            if (s >= 0)
+            if (s >= 0 && s < prm.nsel)
                 for (int d = 0; d < 3; d++) out[3 * (size_t)s + d] = __uint_as_float(load_be32(q + 12 * a + 4 * d));
         }
         return finish(kOk);
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(kDecodeThreads) xtc_decode_kernel(const Decode
     const float inv = __fdiv_rn(1.0f, precision);
     auto emit = [&](int atom, const int32_t c[3]) {
         const int s = slot ? slot[atom] : atom;
-        if (s >= 0) {
+        if (s >= 0 && s < prm.nsel) {   // (a slot outside the output is ignored rather than written)
             float* o = out + 3 * (size_t)s;
             o[0] = (float)c[0] * inv; o[1] = (float)c[1] * inv; o[2] = (float)c[2] * inv;
         }
