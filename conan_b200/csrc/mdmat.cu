@@ -340,12 +340,14 @@ __device__ __forceinline__ int fast_pair(const MdmatParams& prm, const float* __
                                          const float* __restrict__ aJp, int pstride, float4 si, float4 sj,
                                          int ci, int cj, const float* __restrict__ box) {
     float Dx = sj.x - si.x, Dy = sj.y - si.y, Dz = sj.z - si.z;
-    // box = the three box lengths of the frame.  Only pairs whose spheres stay inside half a box come here, so
+    // box = the three box lengths of the frame and their reciprocals.  Only pairs whose spheres stay inside half a box come here, so
     // the centre difference is well clear of +-L/2 and the nearest-image shift can be taken by rounding.
     bool shifted = false;
     if (PBC) {
         const float Rx = Dx, Ry = Dy, Rz = Dz;
-        Dx = nearest_image(Dx, box[0]); Dy = nearest_image(Dy, box[1]); Dz = nearest_image(Dz, box[2]);
+        Dx = fmaf(-rintf(Dx * box[3]), box[0], Dx);     // box[3..5] = 1 / L
+        Dy = fmaf(-rintf(Dy * box[4]), box[1], Dy);
+        Dz = fmaf(-rintf(Dz * box[5]), box[2], Dz);
         shifted = Dx != Rx || Dy != Ry || Dz != Rz;
     }
     const float rr = si.w + sj.w;
@@ -393,7 +395,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     int* rowbase = counters + 6;                        // [64] element index of pair (row residue, residue 0) in a frame row
     int* origI = rowbase + kTile;                       // [64] residue at row position i / column position j of the tile
     int* origJ = origI + kTile;
-    float* boxs = reinterpret_cast<float*>(origJ + kTile);   // [kMaxFB][3] box lengths of the group's frames (periodic runs)
+    float* boxs = reinterpret_cast<float*>(origJ + kTile);   // [kMaxFB][6] box lengths of the group's frames and their reciprocals
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t blk = blockIdx.x;
@@ -459,8 +461,10 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     // frame g is its centre in the group's first frame plus the minimum image of the displacement, modulo
     // that frame's box, which is all the torus triangle inequality of the pruning test needs.
     if (PBC && tid >= 2 * kTile && tid < 2 * kTile + nfb * 3) {
-        const int q = tid - 2 * kTile;
-        boxs[q] = prm.box[9 * (f0 + q / 3) + 4 * (q % 3)];
+        const int q = tid - 2 * kTile, g = q / 3, c = q % 3;
+        const float L = prm.box[9 * (f0 + g) + 4 * c];
+        boxs[6 * g + c] = L;
+        boxs[6 * g + 3 + c] = L > 0.f ? 1.0f / L : 0.f;
     }
     if (tid < 2 * kTile) {
         const bool isI = tid < kTile;
@@ -477,7 +481,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             float dx = sg.x - s0.x, dy = sg.y - s0.y, dz = sg.z - s0.z;
             if (PBC) {
                 const float* b = prm.box + 9 * (f0 + g);
-                dx = min_image(dx, b[0]); dy = min_image(dy, b[4]); dz = min_image(dz, b[8]);
+                dx = nearest_image(dx, b[0]); dy = nearest_image(dy, b[4]); dz = nearest_image(dz, b[8]);
             }
             R = fmaxf(R, sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx))) * 1.000001f + sg.w);
         }
@@ -539,7 +543,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             if (!PBC || !(e & 0x1000))
                 level = fast_pair<PBC>(prm, aI + (size_t)g * kPlanesI * pstride + i, aJ + (size_t)g * kPlanesJ * pstride + j,
                                        pstride, sphI[g * kTile + i], sphJ[g * kTile + j], ci, cj,
-                                       PBC ? boxs + 3 * g : nullptr);
+                                       PBC ? boxs + 6 * g : nullptr);
             if (level < 0) {
                 const int k = atom_add_shared(&counters[1], 1);
                 if (k < kSlowCap) {
@@ -563,8 +567,14 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             const int i = e & 63, j = (e >> 6) & 63, g = e >> 13;
             float Lx = 0.f, Ly = 0.f, Lz = 0.f;
             if (PBC) {
-                const float* b = prm.box + 9 * (f0 + g);
-                Lx = b[0]; Ly = b[4]; Lz = b[8];
+                // A pair whose spheres stay inside half a box and whose centres need no lattice shift has every
+                // atom difference inside (-L/2, L/2): the minimum image leaves it alone, so it is not applied.
+                const float4 a = sphI[g * kTile + i], b = sphJ[g * kTile + j];
+                const float* bl = boxs + 6 * g;
+                const float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
+                const bool image = (e & 0x1000) || nearest_image(dx, bl[0]) != dx || nearest_image(dy, bl[1]) != dy ||
+                                   nearest_image(dz, bl[2]) != dz;
+                if (image) { Lx = bl[0]; Ly = bl[1]; Lz = bl[2]; }
             }
             const int level = exact_pair_warp(prm, f0 + g, origI[i], origJ[j], Lx, Ly, Lz, lane, near);
             if (lane == 0)
@@ -590,10 +600,11 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         if (PBC) {
             Lx = boxs[0]; Ly = boxs[1]; Lz = boxs[2];
             for (int q = 1; q < nfb; q++) {
-                same_box = same_box && boxs[3 * q] == boxs[0] && boxs[3 * q + 1] == boxs[1] && boxs[3 * q + 2] == boxs[2];
-                Lx = fminf(Lx, boxs[3 * q]); Ly = fminf(Ly, boxs[3 * q + 1]); Lz = fminf(Lz, boxs[3 * q + 2]);
+                same_box = same_box && boxs[6 * q] == boxs[0] && boxs[6 * q + 1] == boxs[1] && boxs[6 * q + 2] == boxs[2];
+                Lx = fminf(Lx, boxs[6 * q]); Ly = fminf(Ly, boxs[6 * q + 1]); Lz = fminf(Lz, boxs[6 * q + 2]);
             }
         }
+        const float iLx = Lx > 0.f ? 1.0f / Lx : 0.f, iLy = Ly > 0.f ? 1.0f / Ly : 0.f, iLz = Lz > 0.f ? 1.0f / Lz : 0.f;
         // The tile is taken in 16 x 16 sub-blocks, two per warp.  Rows and columns are sorted by residue
         // size (block_perm_kernel), so the pairs of a sub-block have similar numbers of atoms on both
         // sides; a sub-block's survivors go into the list as one contiguous run (one reservation), and the
@@ -619,14 +630,16 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 if (PBC) {
                     // the distance of the group centres on the torus: per component the smallest minimum
                     // image over the frames' boxes (one evaluation when the box does not change)
+                    // (rounding to the nearest image instead of gmx's loop: the pruning distance carries a
+                    // relative slack of 1e-5, far above the difference)
                     if (same_box) {
-                        dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz);
+                        dx = fmaf(-rintf(dx * iLx), Lx, dx); dy = fmaf(-rintf(dy * iLy), Ly, dy); dz = fmaf(-rintf(dz * iLz), Lz, dz);
                     } else {
                         float mx = 3.0e38f, my = 3.0e38f, mz = 3.0e38f;
                         for (int q = 0; q < nfb; q++) {
-                            mx = fminf(mx, fabsf(min_image(dx, boxs[3 * q])));
-                            my = fminf(my, fabsf(min_image(dy, boxs[3 * q + 1])));
-                            mz = fminf(mz, fabsf(min_image(dz, boxs[3 * q + 2])));
+                            mx = fminf(mx, fabsf(nearest_image(dx, boxs[6 * q])));
+                            my = fminf(my, fabsf(nearest_image(dy, boxs[6 * q + 1])));
+                            mz = fminf(mz, fabsf(nearest_image(dz, boxs[6 * q + 2])));
                         }
                         dx = mx; dy = my; dz = mz;
                     }
@@ -698,7 +711,7 @@ size_t mdmat_smem_bytes(int kpad, int fb) {
     s += 2 * kTile * sizeof(int);                               // counts
     s += (size_t)(kListCap + kSlowCap) * sizeof(uint16_t);      // survivor and redo lists
     s += 8 + 6 * sizeof(int) + 3 * kTile * sizeof(int);         // mbarrier + counters + row bases + residue numbers
-    s += kMaxFB * 3 * sizeof(float);                            // box lengths of the group's frames
+    s += kMaxFB * 6 * sizeof(float);                            // box lengths of the group's frames and reciprocals
     return (s + 15) & ~(size_t)15;
 }
 
