@@ -71,6 +71,38 @@ def test_minimum_image_across_the_box(lib, orc):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("npt", [False, True])
+def test_whole_residues_wrapped_into_a_box(lib, orc, npt):
+    """Residues kept whole but wrapped into the box frame by frame, so they jump across it inside a frame group
+    and many contacts need a lattice shift in the fast path; with npt the box changes from frame to frame
+    (the pruning then takes the smallest image over the group's boxes)."""
+    from conan_b200 import stage1, synth
+    nf = 8
+    xyz, res_start, _ = synth.make_trajectory(150, nf, seed=12)
+    xyz = xyz + np.linspace(0.0, 1.3, nf, dtype=np.float32)[:, None, None]      # a drift, so residues cross the faces
+    lengths = 5.0 * (1.0 + (0.002 * np.arange(nf) if npt else np.zeros(nf)))
+    boxes = np.zeros((nf, 3, 3), np.float32)
+    wrapped = np.empty_like(xyz)
+    for f in range(nf):
+        boxes[f] = np.eye(3, dtype=np.float32) * np.float32(lengths[f])
+        L = float(boxes[f, 0, 0])
+        for r in range(len(res_start) - 1):
+            a, b = res_start[r], res_start[r + 1]
+            c = xyz[f, a:b].mean(axis=0)
+            wrapped[f, a:b] = xyz[f, a:b] - np.floor(c / L).astype(np.float32) * np.float32(L)
+    wrapped = wrapped.astype(np.float32)
+    want = orc.condensed(orc.mdmat_levels(wrapped, boxes, np.arange(xyz.shape[1]), res_start, 1.0, 1001, 1))
+    plain = orc.condensed(orc.mdmat_levels(wrapped, boxes, np.arange(xyz.shape[1]), res_start, 1.0, 1001, 0))
+    assert (want != plain).sum() > 200                   # the periodic images matter here
+    got, _ = _levels(wrapped, boxes, stage1.Geometry(res_start), 1.0, 1001, pbc=True)
+    assert np.array_equal(got, want)
+    # and as an X x Y block
+    geom = stage1.Geometry(res_start, x0=10, xres=70, y0=60, yres=90)
+    got, _ = _levels(wrapped, boxes, geom, 1.0, 1001, pbc=True)
+    full = orc.mdmat_levels(wrapped, boxes, np.arange(xyz.shape[1]), res_start, 1.0, 1001, 1)
+    assert np.array_equal(got, orc.block(full, 10, 70, 60, 90))
+
+
 def test_edge_sizes(lib, orc):
     from conan_b200 import stage1
     rng = np.random.default_rng(2)
