@@ -285,7 +285,12 @@ def run_ours(args):
 
     # ---- end to end from host memory --------------------------------------------------------
     batch = max(1, min(args.batch, nf))
-    nb = (nf + batch - 1) // batch
+    # the first copy cannot hide behind compute, so the batches start small and double up to the full size
+    edges, size = [0], min(batch, 128)
+    while edges[-1] < nf:
+        edges.append(min(nf, edges[-1] + size))
+        size = min(batch, size * 2)
+    nb = len(edges) - 1
     stage_buf = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(2)]
     work_b = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
     copy_stream = torch.cuda.Stream(dev)
@@ -294,19 +299,22 @@ def run_ours(args):
     d2h_bytes = sum(t.numel() * t.element_size() for t in host_out.values())
     h2d_bytes = h_xyz.numel() * 4
 
+    last_use = [None, None]      # the event after the last kernel that read each staging buffer (also across steps)
+
     def step_e2e():
         copied = [torch.cuda.Event() for _ in range(nb)]
         consumed = [torch.cuda.Event() for _ in range(nb)]
         for b in range(nb):
-            b0, b1 = b * batch, min(nf, (b + 1) * batch)
+            b0, b1 = edges[b], edges[b + 1]
             with torch.cuda.stream(copy_stream):
-                if b >= 2:
-                    copy_stream.wait_event(consumed[b - 2])
+                if last_use[b % 2] is not None:
+                    copy_stream.wait_event(last_use[b % 2])
                 stage_buf[b % 2][: b1 - b0].copy_(h_xyz[b0:b1], non_blocking=True)
                 copied[b].record(copy_stream)
             stream.wait_event(copied[b])
             stage1.mdmat_frames(stage_buf[b % 2][: b1 - b0], None, geom, TRUNC, NLEVELS, False, levels[b0:b1], work_b, None)
             consumed[b].record(stream)
+            last_use[b % 2] = consumed[b]
         if world > 1:
             sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
         else:
