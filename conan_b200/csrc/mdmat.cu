@@ -49,6 +49,7 @@ constexpr int kListCap = 4608;     // survivor list entries (a frame adds at mos
 constexpr int kSlowCap = 512;      // pairs waiting for the exact path
 constexpr int kSmemBudget = 74 * 1024;   // keeps three CTAs per SM
 constexpr float kPruneSlack = 1.00001f;
+constexpr int kSphereIters = 16;          // steps of the bounding-sphere refinement in prep_slots_kernel
 constexpr float kErrC = 64.0f * 5.9604645e-8f;   // rounding bound of the expanded form, see fast_pair()
 
 __host__ __device__ inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
@@ -70,6 +71,9 @@ __global__ void block_perm_kernel(const int* __restrict__ res_start, int nres, i
     perm[blockIdx.x * kTile + pos] = r;
 }
 
+// KP > 0: residues have at most KP atoms and a thread keeps its residue in registers (one pass over global
+// memory); KP = 0: any size, the atoms are re-read from global memory for every pass.
+template <int KP>
 __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __restrict__ res_start,
                                   const int* __restrict__ perm, int64_t nf, int natoms, int nres, int nres_pad,
                                   int kpad, float* __restrict__ slots, float4* __restrict__ sph,
@@ -92,20 +96,71 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
     const int a0 = res_start[r], a1 = res_start[r + 1];
     const int n = a1 - a0;
     const float* x = xyz + ((size_t)f * natoms + a0) * 3;
+    constexpr int KR = KP > 0 ? KP : 1;
+    float ax[KR], ay[KR], az[KR];
+    if (KP > 0) {
+#pragma unroll
+        for (int k = 0; k < KR; k++) {
+            const int kk = k < n ? k : 0;               // slots past the residue repeat its first atom
+            ax[k] = x[3 * kk]; ay[k] = x[3 * kk + 1]; az[k] = x[3 * kk + 2];
+        }
+    }
+    auto atom = [&](int k, float& px, float& py, float& pz) {
+        if (KP > 0) { px = ax[k]; py = ay[k]; pz = az[k]; }
+        else { px = x[3 * k]; py = x[3 * k + 1]; pz = x[3 * k + 2]; }
+    };
     float sx = 0.f, sy = 0.f, sz = 0.f;
-    for (int k = 0; k < n; k++) { sx += x[3 * k]; sy += x[3 * k + 1]; sz += x[3 * k + 2]; }
+    if (KP > 0) {
+#pragma unroll
+        for (int k = 0; k < KR; k++)
+            if (k < n) { sx += ax[k]; sy += ay[k]; sz += az[k]; }
+    } else {
+        for (int k = 0; k < n; k++) { sx += x[3 * k]; sy += x[3 * k + 1]; sz += x[3 * k + 2]; }
+    }
     const float inv = 1.0f / (float)n;
-    const float cx = sx * inv, cy = sy * inv, cz = sz * inv;
+    float cx = sx * inv, cy = sy * inv, cz = sz * inv;
+    // A tighter bounding sphere than the one around the centroid (Badoiu-Clarkson: a few steps towards the
+    // farthest atom with shrinking step length): every 1 % off the radii takes about 1 % of the residue pairs
+    // off the survivor lists.  Any centre is valid; the slots are stored relative to it.
+#pragma unroll 1
+    for (int it = 1; it <= kSphereIters; it++) {
+        float best = -1.f, fx = 0.f, fy = 0.f, fz = 0.f;
+        if (KP > 0) {
+#pragma unroll
+            for (int k = 0; k < KR; k++) {              // (repeated slots cannot win against the atom they repeat)
+                const float px = ax[k] - cx, py = ay[k] - cy, pz = az[k] - cz;
+                const float d2 = fmaf(pz, pz, fmaf(py, py, px * px));
+                if (d2 > best) { best = d2; fx = px; fy = py; fz = pz; }
+            }
+        } else {
+            for (int k = 0; k < n; k++) {
+                const float px = x[3 * k] - cx, py = x[3 * k + 1] - cy, pz = x[3 * k + 2] - cz;
+                const float d2 = fmaf(pz, pz, fmaf(py, py, px * px));
+                if (d2 > best) { best = d2; fx = px; fy = py; fz = pz; }
+            }
+        }
+        const float w = 1.0f / (float)(it + 1);
+        cx = fmaf(fx, w, cx); cy = fmaf(fy, w, cy); cz = fmaf(fz, w, cz);
+    }
     float r2max = 0.f;
-    for (int k = 0; k < kpad; k++) {
-        const int kk = k < n ? k : 0;
-        const float px = x[3 * kk] - cx, py = x[3 * kk + 1] - cy, pz = x[3 * kk + 2] - cz;
+    auto emit = [&](int k, float qx, float qy, float qz) {
+        const float px = qx - cx, py = qy - cy, pz = qz - cz;
         const float n2 = fmaf(pz, pz, fmaf(py, py, px * px));
         r2max = fmaxf(r2max, n2);
         float* o = sl + k * kstride;
         o[0] = px; o[pstride] = py; o[2 * pstride] = pz;
         o[3 * pstride] = -2.f * px; o[4 * pstride] = -2.f * py; o[5 * pstride] = -2.f * pz;
         o[6 * pstride] = n2;
+    };
+    if (KP > 0) {
+#pragma unroll
+        for (int k = 0; k < KR; k++)
+            if (k < kpad) emit(k, ax[k], ay[k], az[k]);
+    } else {
+        for (int k = 0; k < kpad; k++) {
+            const int kk = k < n ? k : 0;
+            emit(k, x[3 * kk], x[3 * kk + 1], x[3 * kk + 2]);
+        }
     }
     sph[(size_t)f * nres_pad + pos] = make_float4(cx, cy, cz, sqrtf(r2max) * 1.000001f);
     if (f == 0) cnt[pos] = n;
@@ -806,8 +861,16 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
         block_perm_kernel<<<(unsigned)(L.nres_pad / kTile), kTile, 0, stream>>>(d_res_start, nres, d_perm);
         const int64_t total = nf * L.nres_pad;
         const int threads = 128;
-        prep_slots_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, stream>>>(
-            d_xyz, d_res_start, d_perm, nf, natoms, nres, L.nres_pad, L.kpad, d_slots, d_sph, d_cnt);
+        const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+        if (L.kpad <= 8)
+            prep_slots_kernel<8><<<blocks, threads, 0, stream>>>(d_xyz, d_res_start, d_perm, nf, natoms, nres, L.nres_pad,
+                                                                 L.kpad, d_slots, d_sph, d_cnt);
+        else if (L.kpad <= 16)
+            prep_slots_kernel<16><<<blocks, threads, 0, stream>>>(d_xyz, d_res_start, d_perm, nf, natoms, nres, L.nres_pad,
+                                                                  L.kpad, d_slots, d_sph, d_cnt);
+        else
+            prep_slots_kernel<0><<<blocks, threads, 0, stream>>>(d_xyz, d_res_start, d_perm, nf, natoms, nres, L.nres_pad,
+                                                                 L.kpad, d_slots, d_sph, d_cnt);
         CONAN_CUDA_TRY(cudaGetLastError());
     }
     if (!(phases & 2)) return CONAN_OK;
