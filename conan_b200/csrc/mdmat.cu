@@ -529,18 +529,35 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         const float4* src = prm.sph + (size_t)f0 * prm.nres_pad + gr;
         const float4 s0 = src[0];
         dst[l] = s0;
-        float R = s0.w;
-        for (int g = 1; g < nfb; g++) {
-            const float4 sg = src[(size_t)g * prm.nres_pad];
-            dst[g * kTile + l] = sg;
-            float dx = sg.x - s0.x, dy = sg.y - s0.y, dz = sg.z - s0.z;
-            if (PBC) {
-                const float* b = prm.box + 9 * (f0 + g);
-                dx = nearest_image(dx, b[0]); dy = nearest_image(dy, b[4]); dz = nearest_image(dz, b[8]);
+        // displacements of the centre since the group's first frame, and the group sphere around their mean
+        float ux[kMaxFB], uy[kMaxFB], uz[kMaxFB], rw[kMaxFB];
+        float mx = 0.f, my = 0.f, mz = 0.f;
+        ux[0] = uy[0] = uz[0] = 0.f; rw[0] = s0.w;
+#pragma unroll
+        for (int g = 1; g < kMaxFB; g++) {
+            ux[g] = uy[g] = uz[g] = 0.f; rw[g] = 0.f;
+            if (g < nfb) {
+                const float4 sg = src[(size_t)g * prm.nres_pad];
+                dst[g * kTile + l] = sg;
+                float dx = sg.x - s0.x, dy = sg.y - s0.y, dz = sg.z - s0.z;
+                if (PBC) {
+                    const float* b = prm.box + 9 * (f0 + g);
+                    dx = nearest_image(dx, b[0]); dy = nearest_image(dy, b[4]); dz = nearest_image(dz, b[8]);
+                }
+                ux[g] = dx; uy[g] = dy; uz[g] = dz; rw[g] = sg.w;
+                mx += dx; my += dy; mz += dz;
             }
-            R = fmaxf(R, sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx))) * 1.000001f + sg.w);
         }
-        (isI ? grpI : grpJ)[l] = make_float4(s0.x, s0.y, s0.z, R);
+        const float invn = 1.0f / (float)nfb;
+        mx *= invn; my *= invn; mz *= invn;
+        float R = 0.f;
+#pragma unroll
+        for (int g = 0; g < kMaxFB; g++)
+            if (g < nfb) {
+                const float dx = ux[g] - mx, dy = uy[g] - my, dz = uz[g] - mz;
+                R = fmaxf(R, sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx))) * 1.000001f + 1.0e-6f + rw[g]);
+            }
+        (isI ? grpI : grpJ)[l] = make_float4(s0.x + mx, s0.y + my, s0.z + mz, R);
         (isI ? cntI : cntJ)[l] = prm.cnt[gr];
         const int res = prm.perm[gr];
         (isI ? origI : origJ)[l] = res;
