@@ -566,12 +566,12 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
 
     // ---- fill: every pair of the tile starts at the "beyond trunc" level -------------------
     {
-        // half a warp per row: 16 lanes x 4 levels (one 8-byte store) cover the 64 columns
-        const int sub = lane >> 4, l16 = lane & 15;
+        // a quarter of a warp per row: 8 lanes x 8 levels (one 16-byte store) cover the 64 columns
+        const int sub = lane >> 3, l8 = lane & 7;
         const uint32_t fillv = (uint32_t)maxlevel * 0x00010001u;
         const int jlo0 = max(0, j_beg - gj0), jhi = min(kTile, j_end - gj0);
         const uint16_t ml = (uint16_t)maxlevel;
-        for (int i = warp * 2 + sub; i < kTile; i += 2 * kWarps) {
+        for (int i = warp * 4 + sub; i < kTile; i += 4 * kWarps) {
             const int gi = gi0 + i;
             if (gi < i_beg || gi >= i_end) continue;
             const int jlo = diag ? max(jlo0, i + 1) : jlo0;
@@ -579,14 +579,14 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             if (n <= 0) continue;
             uint16_t* p = prm.levels + (size_t)f0 * prm.stride + pair_idx(gi, gj0) + jlo;
             for (int g = 0; g < nfb; g++, p += prm.stride) {
-                // 8-byte aligned body, scalar head and tail
-                const int mis = (int)((reinterpret_cast<uintptr_t>(p) >> 1) & 3);   // elements past alignment
-                const int head = min((4 - mis) & 3, n);
-                const int nq = (n - head) >> 2;
-                if (l16 < head) p[l16] = ml;
-                if (l16 < nq) *reinterpret_cast<uint2*>(p + head + 4 * l16) = make_uint2(fillv, fillv);
-                const int tail0 = head + 4 * nq;
-                if (l16 < n - tail0) p[tail0 + l16] = ml;
+                // 16-byte aligned body, scalar head and tail (up to seven elements each)
+                const int mis = (int)((reinterpret_cast<uintptr_t>(p) >> 1) & 7);   // elements past alignment
+                const int head = min((8 - mis) & 7, n);
+                const int nq = (n - head) >> 3;
+                if (l8 < head) p[l8] = ml;
+                if (l8 < nq) *reinterpret_cast<uint4*>(p + head + 8 * l8) = make_uint4(fillv, fillv, fillv, fillv);
+                const int tail0 = head + 8 * nq;
+                if (l8 < n - tail0) p[tail0 + l8] = ml;
             }
         }
     }
