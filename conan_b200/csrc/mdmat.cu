@@ -5,25 +5,26 @@
 // together with the text parse of dmf.xpm (conan.py:455-567): the uint16 level stack written
 // here is what read_frame would have looked up in dict_legend.
 //
-// Two kernels:
-//   prep_slots_kernel   [nf][natoms][3] coordinates -> a TMA-friendly "slot" layout
-//                       slots[f][plane][k][res]: every residue's atoms relative to the residue's own
-//                       centre, once as (x', y', z') and once pre-scaled for the expanded distance
-//                       form as (-2x', -2y', -2z', |a'|^2); k = atom slot inside the residue,
-//                       residues padded to a multiple of the tile, empty slots repeat the residue's
-//                       first atom (a minimum over slots is unaffected); plus one bounding sphere
-//                       (centre, radius) per residue.
+// Three kernels:
+//   block_perm_kernel   orders the residues of every block of 64 by their number of atoms.
+//   prep_slots_kernel   [nf][natoms][3] coordinates -> a TMA-friendly "slot" layout: every residue's atoms
+//                       relative to the centre of a near-minimal bounding sphere, once as (x', y', z')
+//                       ([frame][plane][k][residue], the column role) and once pre-scaled for the expanded
+//                       distance form as (-2x', -2y', -2z', |a'|^2) ([frame][plane][residue][k], the row
+//                       role); k = atom slot inside the residue, residues padded to a multiple of the tile,
+//                       empty slots repeat the residue's first atom (a minimum over slots is unaffected);
+//                       plus the bounding sphere (centre, radius) per residue.
 //   mdmat_tile_kernel   one CTA per (64x64 residue tile, group of up to 4 consecutive frames).
 //                       Thread 0 issues two TMA tile loads (cp.async.bulk.tensor.4d) covering the
 //                       whole frame group; meanwhile the CTA fills its part of the output with the
-//                       "beyond trunc" level and prunes residue pairs by bounding sphere, compacting
-//                       the survivors of all frames into one shared-memory list.  Survivors are
-//                       evaluated in the expanded form |b'+D|^2 - 2a'.(b'+D) + |a'|^2 (3 FMA + 1 min
-//                       per atom pair) with a rigorous rounding bound E; if every value in
-//                       [m-E, m+E] quantises to the same level that level is final, otherwise the
+//                       "beyond trunc" level and prunes residue pairs by bounding sphere (one sphere per
+//                       residue for the whole group), compacting the survivors into one shared-memory list.
+//                       Survivors are evaluated in the expanded form |b'+D|^2 - 2a'.(b'+D) + |a'|^2 (packed
+//                       FFMA2 product sums, three-input minima) with a rigorous rounding bound E; if every
+//                       value in [m-E, m+E] quantises to the same level that level is final, otherwise the
 //                       pair is redone with the reference operation order (no FMA contraction) from
-//                       the original coordinates, which is also the path for pairs that may need a
-//                       periodic shift.  Results are therefore bit-identical to the CPU restatement.
+//                       the original coordinates, which is also the path for pairs whose atoms may need
+//                       different periodic shifts.  Results are therefore bit-identical to the CPU restatement.
 //
 // The kernel is bound by FP32 / integer instruction issue; see DESIGN.md.
 #include <cuda.h>
@@ -85,10 +86,13 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
     const int r = perm[pos];                            // the residue that sits there
     const size_t kstride = (size_t)nres_pad;
     const size_t pstride = (size_t)kpad * nres_pad;
-    float* sl = slots + (size_t)f * kPlanes * pstride + pos;
+    float* sl = slots + (size_t)f * kPlanes * pstride + pos;                                   // column role: [plane][k][residue]
+    float* slI = slots + (size_t)f * kPlanes * pstride + kPlanesJ * pstride + (size_t)pos * kpad;   // row role: [plane][residue][k]
     if (r >= nres) {
-        for (int pl = 0; pl < kPlanes; pl++)
+        for (int pl = 0; pl < kPlanesJ; pl++)
             for (int k = 0; k < kpad; k++) sl[pl * pstride + k * kstride] = 0.f;
+        for (int pl = 0; pl < kPlanesI; pl++)
+            for (int k = 0; k < kpad; k++) slI[(size_t)pl * pstride + k] = 0.f;
         sph[(size_t)f * nres_pad + pos] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (f == 0) cnt[pos] = 0;
         return;
@@ -143,19 +147,33 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
         cx = fmaf(fx, w, cx); cy = fmaf(fy, w, cy); cz = fmaf(fz, w, cz);
     }
     float r2max = 0.f;
+    float rx[KR], ry[KR], rz[KR], rn[KR];
     auto emit = [&](int k, float qx, float qy, float qz) {
         const float px = qx - cx, py = qy - cy, pz = qz - cz;
         const float n2 = fmaf(pz, pz, fmaf(py, py, px * px));
         r2max = fmaxf(r2max, n2);
         float* o = sl + k * kstride;
         o[0] = px; o[pstride] = py; o[2 * pstride] = pz;
-        o[3 * pstride] = -2.f * px; o[4 * pstride] = -2.f * py; o[5 * pstride] = -2.f * pz;
-        o[6 * pstride] = n2;
+        if (KP > 0) {       // the row-role values leave as 16-byte stores below
+            rx[k < KR ? k : 0] = -2.f * px; ry[k < KR ? k : 0] = -2.f * py; rz[k < KR ? k : 0] = -2.f * pz; rn[k < KR ? k : 0] = n2;
+        } else {
+            float* oi = slI + k;
+            oi[0] = -2.f * px; oi[pstride] = -2.f * py; oi[2 * pstride] = -2.f * pz;
+            oi[3 * pstride] = n2;
+        }
     };
     if (KP > 0) {
 #pragma unroll
         for (int k = 0; k < KR; k++)
             if (k < kpad) emit(k, ax[k], ay[k], az[k]);
+#pragma unroll
+        for (int k = 0; k < KR; k += 4)
+            if (k < kpad) {     // kpad is a multiple of 4 and the row-role record of a residue is 16-byte aligned
+                *reinterpret_cast<float4*>(slI + k) = make_float4(rx[k], rx[k + 1], rx[k + 2], rx[k + 3]);
+                *reinterpret_cast<float4*>(slI + pstride + k) = make_float4(ry[k], ry[k + 1], ry[k + 2], ry[k + 3]);
+                *reinterpret_cast<float4*>(slI + 2 * pstride + k) = make_float4(rz[k], rz[k + 1], rz[k + 2], rz[k + 3]);
+                *reinterpret_cast<float4*>(slI + 3 * pstride + k) = make_float4(rn[k], rn[k + 1], rn[k + 2], rn[k + 3]);
+            }
     } else {
         for (int k = 0; k < kpad; k++) {
             const int kk = k < n ? k : 0;
@@ -220,7 +238,7 @@ struct MdmatParams {
     const int* perm;         // [nres_pad] residue at each position (sorted by size inside blocks of 64)
     const float* xyz;        // [nf][natoms][3] original coordinates (exact path)
     const float* box;        // [nf][9] or nullptr
-    const float* slots;      // [nf][7][kpad][nres_pad], for the plain-load debug path
+    const float* slots;      // per frame [3][kpad][nres_pad] then [4][nres_pad][kpad], for the plain-load debug path
     uint16_t* levels;        // [nf][stride]
     int64_t stride;          // elements between frames
     unsigned long long* counters;   // [0] near-boundary results [1] un-pruned residue pairs [2] atom pairs evaluated
@@ -280,7 +298,8 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
 }
 
 // Minimum over one chunk of ICH i-atom slots against all cj atoms of residue j, expanded form.
-// aI: i-role planes (-2x', -2y', -2z', |a'|^2) of residue i; aJ: j-role planes (x', y', z') of j;
+// aI: i-role planes (-2x', -2y', -2z', |a'|^2) of residue i, its slots contiguous; aJ: j-role planes (x', y', z')
+// of j, slots 64 floats apart;
 // (Dx, Dy, Dz) = centre_j - centre_i.  Returns min over the chunk of |a - b|^2 (approximately).
 // Each product-sum is a chain of three fused multiply-adds rounded exactly as the scalar form.
 template <int ICH>
@@ -288,14 +307,18 @@ __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, co
                                                 int pstride, int a0, int cj, float Dx, float Dy, float Dz, float m) {
     f32x2 ax[ICH / 2], ay[ICH / 2], az[ICH / 2];
     float mu[ICH];
+    // the row residue's slots lie next to each other ([plane][residue][k]): 16-byte loads, already paired
 #pragma unroll
-    for (int u = 0; u < ICH / 2; u++) {
-        ax[u] = pack2(aI[(a0 + 2 * u) * kTile], aI[(a0 + 2 * u + 1) * kTile]);
-        ay[u] = pack2(aI[pstride + (a0 + 2 * u) * kTile], aI[pstride + (a0 + 2 * u + 1) * kTile]);
-        az[u] = pack2(aI[2 * pstride + (a0 + 2 * u) * kTile], aI[2 * pstride + (a0 + 2 * u + 1) * kTile]);
-        mu[2 * u] = 3.0e38f;
-        mu[2 * u + 1] = 3.0e38f;
+    for (int v = 0; v < ICH / 4; v++) {
+        const float4 qx = *reinterpret_cast<const float4*>(aI + a0 + 4 * v);
+        const float4 qy = *reinterpret_cast<const float4*>(aI + pstride + a0 + 4 * v);
+        const float4 qz = *reinterpret_cast<const float4*>(aI + 2 * pstride + a0 + 4 * v);
+        ax[2 * v] = pack2(qx.x, qx.y); ax[2 * v + 1] = pack2(qx.z, qx.w);
+        ay[2 * v] = pack2(qy.x, qy.y); ay[2 * v + 1] = pack2(qy.z, qy.w);
+        az[2 * v] = pack2(qz.x, qz.y); az[2 * v + 1] = pack2(qz.z, qz.w);
     }
+#pragma unroll
+    for (int u = 0; u < ICH; u++) mu[u] = 3.0e38f;
     // two j atoms per trip, combined with the three-input minimum; slots past cj repeat atom 0 of
     // the residue (prep_slots_kernel) and kpad is a multiple of 4, so the odd trip reads valid data
     const float* jx = aJ;                  // three plane pointers walked two atoms at a time
@@ -321,7 +344,10 @@ __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, co
         }
     }
 #pragma unroll
-    for (int u = 0; u < ICH; u++) m = fminf(m, mu[u] + aI[3 * pstride + (a0 + u) * kTile]);
+    for (int v = 0; v < ICH / 4; v++) {
+        const float4 na = *reinterpret_cast<const float4*>(aI + 3 * pstride + a0 + 4 * v);
+        m = fminf(m, fminf(fminf(mu[4 * v] + na.x, mu[4 * v + 1] + na.y), fminf(mu[4 * v + 2] + na.z, mu[4 * v + 3] + na.w)));
+    }
     return m;
 }
 
@@ -435,7 +461,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int kpad = prm.kpad, fbmax = prm.fb;
     const int pstride = kpad * kTile;                 // floats between planes of one frame's tile
-    float* aI = reinterpret_cast<float*>(smem_raw);                       // [fb][4][kpad][64]
+    float* aI = reinterpret_cast<float*>(smem_raw);                       // [fb][4][64][kpad]
     float* aJ = aI + (size_t)fbmax * kPlanesI * pstride;                  // [fb][3][kpad][64]
     float4* sphI = reinterpret_cast<float4*>(aJ + (size_t)fbmax * kPlanesJ * pstride);   // [fb][64]
     float4* sphJ = sphI + fbmax * kTile;
@@ -495,15 +521,16 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         if (tid == 0) {
             const uint32_t bytes = (uint32_t)fbmax * (kPlanesI + kPlanesJ) * (uint32_t)pstride * 4u;
             mbar_expect_tx(bar, bytes);
-            tma_load_4d(aI, &tmapI, bar, gi0, 0, kPlanesJ, (int)f0);
+            tma_load_4d(aI, &tmapI, bar, 0, gi0, 0, (int)f0);
             tma_load_4d(aJ, &tmapJ, bar, gj0, 0, 0, (int)f0);
         }
     } else {
         for (int g = 0; g < nfb; g++) {
             const float* src = prm.slots + (size_t)(f0 + g) * kPlanes * kpad * prm.nres_pad;
             for (int idx = tid; idx < kPlanesI * pstride; idx += kThreads) {
-                const int r = idx & (kTile - 1), pk = idx >> 6;   // pk = plane*kpad + k
-                aI[(size_t)g * kPlanesI * pstride + idx] = src[(size_t)(pk + kPlanesJ * kpad) * prm.nres_pad + gi0 + r];
+                const int pl = idx / pstride, rk = idx - pl * pstride;   // rk = residue * kpad + k
+                aI[(size_t)g * kPlanesI * pstride + idx] =
+                    src[(size_t)(kPlanesJ + pl) * kpad * prm.nres_pad + (size_t)gi0 * kpad + rk];
             }
             for (int idx = tid; idx < kPlanesJ * pstride; idx += kThreads) {
                 const int r = idx & (kTile - 1), pk = idx >> 6;
@@ -613,7 +640,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             evals += ci * cj;
             int level = -1;
             if (!PBC || !(e & 0x1000))
-                level = fast_pair<PBC>(prm, aI + (size_t)g * kPlanesI * pstride + i, aJ + (size_t)g * kPlanesJ * pstride + j,
+                level = fast_pair<PBC>(prm, aI + (size_t)g * kPlanesI * pstride + i * kpad, aJ + (size_t)g * kPlanesJ * pstride + j,
                                        pstride, sphI[g * kTile + i], sphJ[g * kTile + j], ci, cj,
                                        PBC ? boxs + 6 * g : nullptr);
             if (level < 0) {
@@ -932,18 +959,21 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
         const int64_t nfl = (nf - fbase < frames_per_launch) ? nf - fbase : frames_per_launch;
         // The tensor maps cover only this launch's frames, so coordinate 3 stays small.
         CUtensorMap tmapI, tmapJ;
-        cuuint64_t gdim[4] = {(cuuint64_t)L.nres_pad, (cuuint64_t)L.kpad, (cuuint64_t)kPlanes, (cuuint64_t)nfl};
-        cuuint64_t gstr[3] = {(cuuint64_t)L.nres_pad * 4, (cuuint64_t)L.kpad * L.nres_pad * 4,
-                              (cuuint64_t)kPlanes * L.kpad * L.nres_pad * 4};
-        cuuint32_t boxI[4] = {(cuuint32_t)kTile, (cuuint32_t)L.kpad, (cuuint32_t)kPlanesI, (cuuint32_t)fb};
+        // column role: [frame][3 planes][kpad][residue]; row role (behind it in every frame): [4 planes][residue][kpad]
+        const cuuint64_t frame_bytes = (cuuint64_t)kPlanes * L.kpad * L.nres_pad * 4;
+        cuuint64_t gdimJ[4] = {(cuuint64_t)L.nres_pad, (cuuint64_t)L.kpad, (cuuint64_t)kPlanesJ, (cuuint64_t)nfl};
+        cuuint64_t gstrJ[3] = {(cuuint64_t)L.nres_pad * 4, (cuuint64_t)L.kpad * L.nres_pad * 4, frame_bytes};
+        cuuint64_t gdimI[4] = {(cuuint64_t)L.kpad, (cuuint64_t)L.nres_pad, (cuuint64_t)kPlanesI, (cuuint64_t)nfl};
+        cuuint64_t gstrI[3] = {(cuuint64_t)L.kpad * 4, (cuuint64_t)L.kpad * L.nres_pad * 4, frame_bytes};
+        cuuint32_t boxI[4] = {(cuuint32_t)L.kpad, (cuuint32_t)kTile, (cuuint32_t)kPlanesI, (cuuint32_t)fb};
         cuuint32_t boxJ[4] = {(cuuint32_t)kTile, (cuuint32_t)L.kpad, (cuuint32_t)kPlanesJ, (cuuint32_t)fb};
         cuuint32_t estr[4] = {1, 1, 1, 1};
         float* base = d_slots + (size_t)fbase * kPlanes * L.kpad * L.nres_pad;
-        CUresult cr = encode(&tmapI, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, boxI, estr,
-                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+        CUresult cr = encode(&tmapI, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base + (size_t)kPlanesJ * L.kpad * L.nres_pad, gdimI,
+                             gstrI, boxI, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (cr == CUDA_SUCCESS)
-            cr = encode(&tmapJ, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, boxJ, estr,
+            cr = encode(&tmapJ, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdimJ, gstrJ, boxJ, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (cr != CUDA_SUCCESS)
