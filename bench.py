@@ -291,7 +291,8 @@ def run_ours(args):
         edges.append(min(nf, edges[-1] + size))
         size = min(batch, size * 2)
     nb = len(edges) - 1
-    stage_buf = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(2)]
+    NBUF = 4                     # staging buffers: the copies may run three batches ahead of the kernels
+    stage_buf = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(NBUF)]
     work_b = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
     copy_stream = torch.cuda.Stream(dev)
     host_out = {n: torch.empty(getattr(out, n).shape, dtype=getattr(out, n).dtype).pin_memory()
@@ -299,7 +300,7 @@ def run_ours(args):
     d2h_bytes = sum(t.numel() * t.element_size() for t in host_out.values())
     h2d_bytes = h_xyz.numel() * 4
 
-    last_use = [None, None]      # the event after the last kernel that read each staging buffer (also across steps)
+    last_use = [None] * NBUF     # the event after the last kernel that read each staging buffer (also across steps)
 
     def step_e2e():
         copied = [torch.cuda.Event() for _ in range(nb)]
@@ -307,14 +308,14 @@ def run_ours(args):
         for b in range(nb):
             b0, b1 = edges[b], edges[b + 1]
             with torch.cuda.stream(copy_stream):
-                if last_use[b % 2] is not None:
-                    copy_stream.wait_event(last_use[b % 2])
-                stage_buf[b % 2][: b1 - b0].copy_(h_xyz[b0:b1], non_blocking=True)
+                if last_use[b % NBUF] is not None:
+                    copy_stream.wait_event(last_use[b % NBUF])
+                stage_buf[b % NBUF][: b1 - b0].copy_(h_xyz[b0:b1], non_blocking=True)
                 copied[b].record(copy_stream)
             stream.wait_event(copied[b])
-            stage1.mdmat_frames(stage_buf[b % 2][: b1 - b0], None, geom, TRUNC, NLEVELS, False, levels[b0:b1], work_b, None)
+            stage1.mdmat_frames(stage_buf[b % NBUF][: b1 - b0], None, geom, TRUNC, NLEVELS, False, levels[b0:b1], work_b, None)
             consumed[b].record(stream)
-            last_use[b % 2] = consumed[b]
+            last_use[b % NBUF] = consumed[b]
         if world > 1:
             sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
         else:
