@@ -8,19 +8,20 @@
 // Three kernels:
 //   block_perm_kernel   orders the residues of every block of 64 by their number of atoms.
 //   prep_slots_kernel   [nf][natoms][3] coordinates -> a TMA-friendly "slot" layout: every residue's atoms
-//                       relative to the centre of a near-minimal bounding sphere, once as (x', y', z')
-//                       ([frame][plane][k][residue], the column role) and once pre-scaled for the expanded
-//                       distance form as (-2x', -2y', -2z', |a'|^2) ([frame][plane][residue][k], the row
-//                       role); k = atom slot inside the residue, residues padded to a multiple of the tile,
-//                       empty slots repeat the residue's first atom (a minimum over slots is unaffected);
-//                       plus the bounding sphere (centre, radius) per residue.
-//   mdmat_tile_kernel   one CTA per (64x64 residue tile, group of up to 4 consecutive frames).
+//                       relative to the centre of a near-minimal bounding sphere, four planes
+//                       (x', y', z', |a'|^2) laid out [frame][plane][residue][k]; k = atom slot inside the
+//                       residue (a residue's slots are contiguous, so both roles read them with 16-byte
+//                       loads), residues padded to a multiple of the tile, empty slots repeat the residue's
+//                       first atom (a minimum over slots is unaffected); plus the bounding sphere (centre,
+//                       radius) per residue.
+//   mdmat_tile_kernel   one CTA per (64x64 residue tile, group of consecutive frames).
 //                       Thread 0 issues two TMA tile loads (cp.async.bulk.tensor.4d) covering the
 //                       whole frame group; meanwhile the CTA fills its part of the output with the
 //                       "beyond trunc" level and prunes residue pairs by bounding sphere (one sphere per
 //                       residue for the whole group), compacting the survivors into one shared-memory list.
-//                       Survivors are evaluated in the expanded form |b'+D|^2 - 2a'.(b'+D) + |a'|^2 (packed
-//                       FFMA2 product sums, three-input minima) with a rigorous rounding bound E; if every
+//                       Survivors are evaluated in the expanded form |b'|^2 - 2a".b' + |a"|^2 with the row
+//                       atoms moved into the column residue's frame (a" = a' - D, D = centre_j - centre_i),
+//                       as packed FFMA2 product sums and three-input minima, with a rigorous rounding bound E; if every
 //                       value in [m-E, m+E] quantises to the same level that level is final, otherwise the
 //                       pair is redone with the reference operation order (no FMA contraction) from
 //                       the original coordinates, which is also the path for pairs whose atoms may need
@@ -40,18 +41,14 @@
 namespace {
 
 constexpr int kTile = 64;          // residues per tile side
-constexpr int kThreads = 256;      // threads per CTA of mdmat_tile_kernel
-constexpr int kWarps = kThreads / 32;
-constexpr int kMaxKpad = 128;      // largest supported atoms-per-residue (after padding to 4)
-constexpr int kMaxFB = 4;          // frames per CTA at most (2 bits in a list entry)
-constexpr int kPlanes = 7;         // x' y' z' | -2x' -2y' -2z' |a'|^2
-constexpr int kPlanesJ = 3, kPlanesI = 4;
-constexpr int kListCap = 4608;     // survivor list entries (a frame adds at most 4096)
-constexpr int kSlowCap = 512;      // pairs waiting for the exact path
-constexpr int kSmemBudget = 74 * 1024;   // keeps three CTAs per SM
+constexpr int kMaxFB = 8;          // frames per CTA at most (3 bits in a redo-list entry)
+constexpr int kPlanes = 4;         // x' y' z' |a'|^2
+constexpr int kPlanesJ = 4, kPlanesI = 3;   // planes staged per tile side: columns need |b'|^2, rows do not
+constexpr int kListCap = 4096;     // survivor list entries (one per residue pair of the tile)
+constexpr int kSmemLimit = 227 * 1024;   // opt-in shared memory per CTA on sm_100
 constexpr float kPruneSlack = 1.00001f;
 constexpr int kSphereIters = 16;          // steps of the bounding-sphere refinement in prep_slots_kernel
-constexpr float kErrC = 64.0f * 5.9604645e-8f;   // rounding bound of the expanded form, see fast_pair()
+constexpr float kErrC = 1.25f * 5.9604645e-8f;   // safety factor times the unit roundoff, see fast_pair()
 
 __host__ __device__ inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
@@ -84,15 +81,11 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
     int64_t f = gid / nres_pad;
     const int pos = (int)(gid - f * nres_pad);         // position in the padded, per-block sorted order
     const int r = perm[pos];                            // the residue that sits there
-    const size_t kstride = (size_t)nres_pad;
-    const size_t pstride = (size_t)kpad * nres_pad;
-    float* sl = slots + (size_t)f * kPlanes * pstride + pos;                                   // column role: [plane][k][residue]
-    float* slI = slots + (size_t)f * kPlanes * pstride + kPlanesJ * pstride + (size_t)pos * kpad;   // row role: [plane][residue][k]
+    const size_t pstride = (size_t)kpad * nres_pad;     // floats per plane
+    float* sl = slots + (size_t)f * kPlanes * pstride + (size_t)pos * kpad;   // [plane][residue][k]
     if (r >= nres) {
-        for (int pl = 0; pl < kPlanesJ; pl++)
-            for (int k = 0; k < kpad; k++) sl[pl * pstride + k * kstride] = 0.f;
-        for (int pl = 0; pl < kPlanesI; pl++)
-            for (int k = 0; k < kpad; k++) slI[(size_t)pl * pstride + k] = 0.f;
+        for (int pl = 0; pl < kPlanes; pl++)
+            for (int k = 0; k < kpad; k++) sl[(size_t)pl * pstride + k] = 0.f;
         sph[(size_t)f * nres_pad + pos] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (f == 0) cnt[pos] = 0;
         return;
@@ -109,10 +102,6 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
             ax[k] = x[3 * kk]; ay[k] = x[3 * kk + 1]; az[k] = x[3 * kk + 2];
         }
     }
-    auto atom = [&](int k, float& px, float& py, float& pz) {
-        if (KP > 0) { px = ax[k]; py = ay[k]; pz = az[k]; }
-        else { px = x[3 * k]; py = x[3 * k + 1]; pz = x[3 * k + 2]; }
-    };
     float sx = 0.f, sy = 0.f, sz = 0.f;
     if (KP > 0) {
 #pragma unroll
@@ -147,37 +136,30 @@ __global__ void prep_slots_kernel(const float* __restrict__ xyz, const int* __re
         cx = fmaf(fx, w, cx); cy = fmaf(fy, w, cy); cz = fmaf(fz, w, cz);
     }
     float r2max = 0.f;
-    float rx[KR], ry[KR], rz[KR], rn[KR];
-    auto emit = [&](int k, float qx, float qy, float qz) {
-        const float px = qx - cx, py = qy - cy, pz = qz - cz;
-        const float n2 = fmaf(pz, pz, fmaf(py, py, px * px));
-        r2max = fmaxf(r2max, n2);
-        float* o = sl + k * kstride;
-        o[0] = px; o[pstride] = py; o[2 * pstride] = pz;
-        if (KP > 0) {       // the row-role values leave as 16-byte stores below
-            rx[k < KR ? k : 0] = -2.f * px; ry[k < KR ? k : 0] = -2.f * py; rz[k < KR ? k : 0] = -2.f * pz; rn[k < KR ? k : 0] = n2;
-        } else {
-            float* oi = slI + k;
-            oi[0] = -2.f * px; oi[pstride] = -2.f * py; oi[2 * pstride] = -2.f * pz;
-            oi[3 * pstride] = n2;
-        }
-    };
     if (KP > 0) {
+        float rx[KR], ry[KR], rz[KR], rn[KR];
 #pragma unroll
-        for (int k = 0; k < KR; k++)
-            if (k < kpad) emit(k, ax[k], ay[k], az[k]);
+        for (int k = 0; k < KR; k++) {
+            const float px = ax[k] - cx, py = ay[k] - cy, pz = az[k] - cz;
+            const float n2 = fmaf(pz, pz, fmaf(py, py, px * px));
+            r2max = fmaxf(r2max, n2);
+            rx[k] = px; ry[k] = py; rz[k] = pz; rn[k] = n2;
+        }
 #pragma unroll
         for (int k = 0; k < KR; k += 4)
-            if (k < kpad) {     // kpad is a multiple of 4 and the row-role record of a residue is 16-byte aligned
-                *reinterpret_cast<float4*>(slI + k) = make_float4(rx[k], rx[k + 1], rx[k + 2], rx[k + 3]);
-                *reinterpret_cast<float4*>(slI + pstride + k) = make_float4(ry[k], ry[k + 1], ry[k + 2], ry[k + 3]);
-                *reinterpret_cast<float4*>(slI + 2 * pstride + k) = make_float4(rz[k], rz[k + 1], rz[k + 2], rz[k + 3]);
-                *reinterpret_cast<float4*>(slI + 3 * pstride + k) = make_float4(rn[k], rn[k + 1], rn[k + 2], rn[k + 3]);
+            if (k < kpad) {     // kpad is a multiple of 4 and a residue's record is 16-byte aligned
+                *reinterpret_cast<float4*>(sl + k) = make_float4(rx[k], rx[k + 1], rx[k + 2], rx[k + 3]);
+                *reinterpret_cast<float4*>(sl + pstride + k) = make_float4(ry[k], ry[k + 1], ry[k + 2], ry[k + 3]);
+                *reinterpret_cast<float4*>(sl + 2 * pstride + k) = make_float4(rz[k], rz[k + 1], rz[k + 2], rz[k + 3]);
+                *reinterpret_cast<float4*>(sl + 3 * pstride + k) = make_float4(rn[k], rn[k + 1], rn[k + 2], rn[k + 3]);
             }
     } else {
         for (int k = 0; k < kpad; k++) {
             const int kk = k < n ? k : 0;
-            emit(k, x[3 * kk], x[3 * kk + 1], x[3 * kk + 2]);
+            const float px = x[3 * kk] - cx, py = x[3 * kk + 1] - cy, pz = x[3 * kk + 2] - cz;
+            const float n2 = fmaf(pz, pz, fmaf(py, py, px * px));
+            r2max = fmaxf(r2max, n2);
+            sl[k] = px; sl[pstride + k] = py; sl[2 * pstride + k] = pz; sl[3 * pstride + k] = n2;
         }
     }
     sph[(size_t)f * nres_pad + pos] = make_float4(cx, cy, cz, sqrtf(r2max) * 1.000001f);
@@ -238,7 +220,7 @@ struct MdmatParams {
     const int* perm;         // [nres_pad] residue at each position (sorted by size inside blocks of 64)
     const float* xyz;        // [nf][natoms][3] original coordinates (exact path)
     const float* box;        // [nf][9] or nullptr
-    const float* slots;      // per frame [3][kpad][nres_pad] then [4][nres_pad][kpad], for the plain-load debug path
+    const float* slots;      // per frame [4][nres_pad][kpad], for the plain-load debug path
     uint16_t* levels;        // [nf][stride]
     int64_t stride;          // elements between frames
     unsigned long long* counters;   // [0] near-boundary results [1] un-pruned residue pairs [2] atom pairs evaluated
@@ -253,6 +235,8 @@ struct MdmatParams {
     int maxlevel;
     int pbc;
     int use_tma;             // 0: stage tiles with plain loads (debug aid, CONAN_MDMAT_NO_TMA=1)
+    int swz;                 // tiles land with the 32-byte TMA swizzle (kpad == 8 only)
+    int dbg;                 // timing experiments only (CONAN_MDMAT_DEBUG): 1 no exact path, 2 no fill, 4 no items, 8 no pruning
 };
 
 __device__ __forceinline__ float min_image(float d, float L) {
@@ -281,7 +265,7 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) {
 }
 
 // Packed FP32 pairs (FFMA2): one issue slot for two fused multiply-adds.  ptxas turns a pair built
-// from the same scalar twice into the broadcast operand form, so only the i side lives in pairs.
+// from the same scalar twice into the broadcast operand form, so only the row side lives in pairs.
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 pack2(float lo, float hi) {
     f32x2 r;
@@ -296,91 +280,98 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
     return d;
 }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
 
-// Minimum over one chunk of ICH i-atom slots against all cj atoms of residue j, expanded form.
-// aI: i-role planes (-2x', -2y', -2z', |a'|^2) of residue i, its slots contiguous; aJ: j-role planes (x', y', z')
-// of j, slots 64 floats apart;
-// (Dx, Dy, Dz) = centre_j - centre_i.  Returns min over the chunk of |a - b|^2 (approximately).
+// Minimum over one chunk of ICH row-atom slots of residue i against all cj atoms of residue j.
+// aI, aJ: plane 0 of the residue's slots ([plane][residue][k], planes pstride floats apart; rows have
+// x' y' z', columns x' y' z' |b'|^2).  The row atoms are first moved into the column residue's frame and
+// pre-scaled, t = -2 (a' - D) with D = centre_j - centre_i (one FFMA2 per packed pair and coordinate), so
+// that the column values are used as they were stored: |a - b|^2 = |b'|^2 + t.b' + |t|^2 / 4.
 // Each product-sum is a chain of three fused multiply-adds rounded exactly as the scalar form.
-template <int ICH>
+// xi / xj: 0, or 4 where the 32-byte TMA swizzle has exchanged the residue's two 16-byte halves.
+// K8: every residue has at most eight slots (kpad == 8), so the column loop is two trips, unrolled.
+template <int ICH, bool K8>
 __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, const float* __restrict__ aJ,
-                                                int pstride, int a0, int cj, float Dx, float Dy, float Dz, float m) {
-    f32x2 ax[ICH / 2], ay[ICH / 2], az[ICH / 2];
+                                                int pstride, int a0, int xi, int xj, int cj, float Dx2, float Dy2,
+                                                float Dz2, float m) {
+    f32x2 tx[ICH / 2], ty[ICH / 2], tz[ICH / 2];
     float mu[ICH];
-    // the row residue's slots lie next to each other ([plane][residue][k]): 16-byte loads, already paired
+    {
+        const f32x2 M2 = pack2(-2.f, -2.f);
+        const f32x2 DX = pack2(Dx2, Dx2), DY = pack2(Dy2, Dy2), DZ = pack2(Dz2, Dz2);
 #pragma unroll
-    for (int v = 0; v < ICH / 4; v++) {
-        const float4 qx = *reinterpret_cast<const float4*>(aI + a0 + 4 * v);
-        const float4 qy = *reinterpret_cast<const float4*>(aI + pstride + a0 + 4 * v);
-        const float4 qz = *reinterpret_cast<const float4*>(aI + 2 * pstride + a0 + 4 * v);
-        ax[2 * v] = pack2(qx.x, qx.y); ax[2 * v + 1] = pack2(qx.z, qx.w);
-        ay[2 * v] = pack2(qy.x, qy.y); ay[2 * v + 1] = pack2(qy.z, qy.w);
-        az[2 * v] = pack2(qz.x, qz.y); az[2 * v + 1] = pack2(qz.z, qz.w);
-    }
-#pragma unroll
-    for (int u = 0; u < ICH; u++) mu[u] = 3.0e38f;
-    // two j atoms per trip, combined with the three-input minimum; slots past cj repeat atom 0 of
-    // the residue (prep_slots_kernel) and kpad is a multiple of 4, so the odd trip reads valid data
-    const float* jx = aJ;                  // three plane pointers walked two atoms at a time
-    const float* jy = aJ + pstride;
-    const float* jz = aJ + 2 * pstride;
-#pragma unroll 1
-    for (int b = 0; b < cj; b += 2, jx += 2 * kTile, jy += 2 * kTile, jz += 2 * kTile) {
-        const float bx = jx[0] + Dx, by = jy[0] + Dy, bz = jz[0] + Dz;
-        const float cx = jx[kTile] + Dx, cy = jy[kTile] + Dy, cz = jz[kTile] + Dz;
-        const float nb = fmaf(bz, bz, fmaf(by, by, bx * bx));
-        const float nc = fmaf(cz, cz, fmaf(cy, cy, cx * cx));
-        const f32x2 BX = pack2(bx, bx), BY = pack2(by, by), BZ = pack2(bz, bz), NB = pack2(nb, nb);
-        const f32x2 CX = pack2(cx, cx), CY = pack2(cy, cy), CZ = pack2(cz, cz), NC = pack2(nc, nc);
-#pragma unroll
-        for (int u = 0; u < ICH / 2; u++) {
-            const f32x2 vb = fma2(az[u], BZ, fma2(ay[u], BY, fma2(ax[u], BX, NB)));
-            const f32x2 vc = fma2(az[u], CZ, fma2(ay[u], CY, fma2(ax[u], CX, NC)));
-            float b0, b1, c0, c1;
-            unpack2(vb, b0, b1);
-            unpack2(vc, c0, c1);
-            mu[2 * u] = fmin3(mu[2 * u], b0, c0);
-            mu[2 * u + 1] = fmin3(mu[2 * u + 1], b1, c1);
+        for (int v = 0; v < ICH / 4; v++) {
+            const int o = (a0 + 4 * v) ^ xi;
+            const float4 qx = *reinterpret_cast<const float4*>(aI + o);
+            const float4 qy = *reinterpret_cast<const float4*>(aI + pstride + o);
+            const float4 qz = *reinterpret_cast<const float4*>(aI + 2 * pstride + o);
+            tx[2 * v] = fma2(pack2(qx.x, qx.y), M2, DX); tx[2 * v + 1] = fma2(pack2(qx.z, qx.w), M2, DX);
+            ty[2 * v] = fma2(pack2(qy.x, qy.y), M2, DY); ty[2 * v + 1] = fma2(pack2(qy.z, qy.w), M2, DY);
+            tz[2 * v] = fma2(pack2(qz.x, qz.y), M2, DZ); tz[2 * v + 1] = fma2(pack2(qz.z, qz.w), M2, DZ);
         }
     }
 #pragma unroll
-    for (int v = 0; v < ICH / 4; v++) {
-        const float4 na = *reinterpret_cast<const float4*>(aI + 3 * pstride + a0 + 4 * v);
-        m = fminf(m, fminf(fminf(mu[4 * v] + na.x, mu[4 * v + 1] + na.y), fminf(mu[4 * v + 2] + na.z, mu[4 * v + 3] + na.w)));
+    for (int u = 0; u < ICH; u++) mu[u] = 3.0e38f;
+    // four column atoms per trip (one 16-byte load per plane), two per three-input minimum; slots past cj
+    // repeat atom 0 of the residue (prep_slots_kernel) and kpad is a multiple of 4, so a trip reads valid data
+#pragma unroll 1
+    for (int b = 0; b < (K8 ? 8 : cj); b += 4) {
+        if (K8 && b >= cj) break;       // residues of up to four atoms: one trip
+        const int o = b ^ xj;
+        const float4 bx = *reinterpret_cast<const float4*>(aJ + o);
+        const float4 by = *reinterpret_cast<const float4*>(aJ + pstride + o);
+        const float4 bz = *reinterpret_cast<const float4*>(aJ + 2 * pstride + o);
+        const float4 bn = *reinterpret_cast<const float4*>(aJ + 3 * pstride + o);
+        {
+            const f32x2 BX = pack2(bx.x, bx.x), BY = pack2(by.x, by.x), BZ = pack2(bz.x, bz.x), NB = pack2(bn.x, bn.x);
+            const f32x2 CX = pack2(bx.y, bx.y), CY = pack2(by.y, by.y), CZ = pack2(bz.y, bz.y), NC = pack2(bn.y, bn.y);
+#pragma unroll
+            for (int u = 0; u < ICH / 2; u++) {
+                const f32x2 vb = fma2(tz[u], BZ, fma2(ty[u], BY, fma2(tx[u], BX, NB)));
+                const f32x2 vc = fma2(tz[u], CZ, fma2(ty[u], CY, fma2(tx[u], CX, NC)));
+                float b0, b1, c0, c1;
+                unpack2(vb, b0, b1);
+                unpack2(vc, c0, c1);
+                mu[2 * u] = fmin3(mu[2 * u], b0, c0);
+                mu[2 * u + 1] = fmin3(mu[2 * u + 1], b1, c1);
+            }
+        }
+        {
+            const f32x2 BX = pack2(bx.z, bx.z), BY = pack2(by.z, by.z), BZ = pack2(bz.z, bz.z), NB = pack2(bn.z, bn.z);
+            const f32x2 CX = pack2(bx.w, bx.w), CY = pack2(by.w, by.w), CZ = pack2(bz.w, bz.w), NC = pack2(bn.w, bn.w);
+#pragma unroll
+            for (int u = 0; u < ICH / 2; u++) {
+                const f32x2 vb = fma2(tz[u], BZ, fma2(ty[u], BY, fma2(tx[u], BX, NB)));
+                const f32x2 vc = fma2(tz[u], CZ, fma2(ty[u], CY, fma2(tx[u], CX, NC)));
+                float b0, b1, c0, c1;
+                unpack2(vb, b0, b1);
+                unpack2(vc, c0, c1);
+                mu[2 * u] = fmin3(mu[2 * u], b0, c0);
+                mu[2 * u + 1] = fmin3(mu[2 * u + 1], b1, c1);
+            }
+        }
+    }
+    // + |a' - D|^2 = |t|^2 / 4 (the scaling is exact), after the minimum: the rounded add is monotonic
+#pragma unroll
+    for (int u = 0; u < ICH / 2; u++) {
+        const f32x2 n2 = fma2(tz[u], tz[u], fma2(ty[u], ty[u], mul2(tx[u], tx[u])));
+        float n0, n1;
+        unpack2(n2, n0, n1);
+        m = fmin3(m, fmaf(n0, 0.25f, mu[2 * u]), fmaf(n1, 0.25f, mu[2 * u + 1]));
     }
     return m;
 }
 
 // The exact path: reference operation order on the original coordinates (with the minimum image
-// when pbc is on).  Returns the level and counts results within 2 ulp of a level boundary.
-__device__ __forceinline__ int exact_pair(const MdmatParams& prm, int64_t f, int gi, int gj, float Lx, float Ly,
-                                          float Lz, int& near) {
-    const int a0 = prm.res_start[gi], a1 = prm.res_start[gi + 1];
-    const int b0 = prm.res_start[gj], b1 = prm.res_start[gj + 1];
-    const float* x = prm.xyz + (size_t)f * prm.natoms * 3;
-    float m = prm.trunc2;
-    for (int a = a0; a < a1; a++) {
-        const float xi = x[3 * a], yi = x[3 * a + 1], zi = x[3 * a + 2];
-        for (int b = b0; b < b1; b++) {
-            float dx = xi - x[3 * b], dy = yi - x[3 * b + 1], dz = zi - x[3 * b + 2];
-            if (prm.pbc) { dx = min_image(dx, Lx); dy = min_image(dy, Ly); dz = min_image(dz, Lz); }
-            m = fminf(m, dist2_exact(dx, dy, dz));
-        }
-    }
-    const float r = __fsqrt_rn(m);
-    const float tq = __fmul_rn(r, prm.invlevel);
-    int c = __float2int_rn(tq);
-    c = max(0, min(c, prm.maxlevel));
-    const float frac = fabsf(tq - rintf(tq));
-    near += (fabsf(frac - 0.5f) <= tq * 2.4e-7f) ? 1 : 0;
-    return c;
-}
-
-// The same for a whole warp working on one residue pair: the atom pairs are dealt out to the lanes
+// when pbc is on), by a whole warp working on one residue pair: the atom pairs are dealt out to the lanes
 // and the minimum is combined with shuffles (a minimum does not depend on the order it is taken in).
 // Every lane returns the level; lane 0 counts the near-boundary result.
 __device__ __forceinline__ int exact_pair_warp(const MdmatParams& prm, int64_t f, int gi, int gj, float Lx, float Ly,
-                                               float Lz, int lane, int& near) {
+                                               float Lz, int lane, int* near_counter) {
     const int a0 = prm.res_start[gi], na = prm.res_start[gi + 1] - a0;
     const int b0 = prm.res_start[gj], nb = prm.res_start[gj + 1] - b0;
     const float* x = prm.xyz + (size_t)f * prm.natoms * 3;
@@ -402,7 +393,7 @@ __device__ __forceinline__ int exact_pair_warp(const MdmatParams& prm, int64_t f
     int c = __float2int_rn(tq);
     c = max(0, min(c, prm.maxlevel));
     const float frac = fabsf(tq - rintf(tq));
-    if (lane == 0) near += (fabsf(frac - 0.5f) <= tq * 2.4e-7f) ? 1 : 0;
+    if (lane == 0 && fabsf(frac - 0.5f) <= tq * 2.4e-7f) atomicAdd(near_counter, 1);
     return c;
 }
 
@@ -416,10 +407,11 @@ __device__ __forceinline__ int atom_add_shared(int* addr, int v) {
 
 // One survivor item: residue pair (i, j) of the tile in frame g of the group.  Returns the level,
 // or -1 if the expanded form cannot certify it (the pair then takes the exact path).
-template <bool PBC>
+// aIp / aJp: plane 0 of residue i / j of the frame's row / column tile.
+template <bool PBC, bool K8>
 __device__ __forceinline__ int fast_pair(const MdmatParams& prm, const float* __restrict__ aIp,
-                                         const float* __restrict__ aJp, int pstride, float4 si, float4 sj,
-                                         int ci, int cj, const float* __restrict__ box) {
+                                         const float* __restrict__ aJp, int pstride, int xi, int xj, float4 si,
+                                         float4 sj, int ci, int cj, const float* __restrict__ box) {
     float Dx = sj.x - si.x, Dy = sj.y - si.y, Dz = sj.z - si.z;
     // box = the three box lengths of the frame and their reciprocals.  Only pairs whose spheres stay inside half a box come here, so
     // the centre difference is well clear of +-L/2 and the nearest-image shift can be taken by rounding.
@@ -433,36 +425,65 @@ __device__ __forceinline__ int fast_pair(const MdmatParams& prm, const float* __
     }
     const float rr = si.w + sj.w;
     const float D2 = fmaf(Dz, Dz, fmaf(Dy, Dy, Dx * Dx));
-    // |computed - reference r2| <= 22 u (rr + |D|)^2 <= 44 u (rr^2 + D2); 64 u leaves margin.
-    float E = kErrC * fmaf(rr, rr, D2);
+    // Error of the expanded form against the reference's r2, term by term (u = 2^-24; Ri, Rj the sphere
+    // radii, A = Ri + |D| >= |a' - D|, M = A + Rj >= every difference vector):
+    //   positions: a', b', D and a' - D each carry u per component, the difference vector is off by
+    //              <= 2 u M and its square by <= 4 u M sqrt(r2);
+    //   the sum:   three rounded steps on partial sums <= Rj (Rj + 2 A), three on |b'|^2 <= Rj^2, three on
+    //              |a' - D|^2 <= A^2, the last add on r2 itself: <= 3 u (M^2 + Rj^2) + u r2;
+    //   reference: its own five roundings, <= 5 u r2.
+    // E = 1.25 u (3 (M^2 + Rj^2) + 4 M sqrt(r2) + 6 r2), evaluated once the minimum is known.
+    const float dn = D2 * rsqrtf(fmaxf(D2, 1.0e-20f));
+    const float M = rr + dn;
+    const float M2R = fmaf(M, M, sj.w * sj.w);
     // a pair that is brought together by a lattice shift: the reference forms a - b (of the size of the box)
     // before shifting, and so does the centre difference here: an extra u * L per component
-    if (PBC && shifted) E += 2.5e-7f * fmaxf(box[0], fmaxf(box[1], box[2])) * (rr + D2 * rsqrtf(fmaxf(D2, 1.0e-12f)) * 1.001f);
+    float Ebox = 0.f;
+    if (PBC && shifted) Ebox = 2.5e-7f * fmaxf(box[0], fmaxf(box[1], box[2])) * (rr + dn * 1.001f);
+    const float Dx2 = Dx + Dx, Dy2 = Dy + Dy, Dz2 = Dz + Dz;
     float m = 3.0e38f;
-    int a0 = 0;
-    while (ci - a0 > 4) { m = chunk_min_fast<8>(aIp, aJp, pstride, a0, cj, Dx, Dy, Dz, m); a0 += 8; }
-    if (ci - a0 > 0) m = chunk_min_fast<4>(aIp, aJp, pstride, a0, cj, Dx, Dy, Dz, m);
-    if (m - E >= prm.trunc2 * 1.000001f) return prm.maxlevel;   // certainly beyond trunc
+    if (K8) {
+        if (ci > 4) m = chunk_min_fast<8, true>(aIp, aJp, pstride, 0, xi, xj, cj, Dx2, Dy2, Dz2, m);
+        else m = chunk_min_fast<4, true>(aIp, aJp, pstride, 0, xi, xj, cj, Dx2, Dy2, Dz2, m);
+    } else {
+        int a0 = 0;
+        while (ci - a0 > 4) { m = chunk_min_fast<8, false>(aIp, aJp, pstride, a0, xi, xj, cj, Dx2, Dy2, Dz2, m); a0 += 8; }
+        if (ci - a0 > 0) m = chunk_min_fast<4, false>(aIp, aJp, pstride, a0, xi, xj, cj, Dx2, Dy2, Dz2, m);
+    }
     const float mm = fmaxf(m, 0.f);
+    // sqrt through the reciprocal square root (2^-22.9 relative) instead of the IEEE sequence; the
+    // certification margin below carries the difference
+    float rs;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(fmaxf(mm, 1.0e-7f)));
+    float sq = mm * rs;
+    sq = fmaf(fmaf(-sq, sq, mm), 0.5f * rs, sq);    // one Newton step: within an ulp of the square root
+    const float E = fmaf(kErrC, fmaf(4.f * M, sq, fmaf(3.f, M2R, 6.f * mm)), Ebox);
+    if (m - E >= prm.trunc2 * 1.000001f) return prm.maxlevel;   // certainly beyond trunc
     if (mm < 1.0e-7f) return -1;
-    const float tq = sqrtf(mm) * prm.invlevel;
-    const float c = rintf(tq);
-    // |sqrt(e) - sqrt(m)| <= E / sqrt(m) for every e in [m-E, m+E]; the level is certain when tq
-    // stays clear of the rounding boundary (x.5) by that much plus the rounding of sqrt and mul
-    const float dt = E * prm.invlevel * rsqrtf(mm) * 1.01f + tq * 4.0e-7f + 1.0e-6f;
-    if (fabsf(fabsf(tq - c) - 0.5f) > dt) return min((int)c, prm.maxlevel);
+    const float tq = sq * prm.invlevel;
+    const float cb = tq + 12582912.f;               // 1.5 * 2^23: rounds tq to the nearest integer (ties to even)
+    const float c = cb - 12582912.f;
+    // |sqrt(e) - sqrt(m)| = |e - m| / (sqrt(e) + sqrt(m)) <= 0.502 E / sqrt(m) for every e in [m-E, m+E]
+    // while E < m / 100 (E / sqrt(m) otherwise); the level is certain when tq stays clear of the rounding
+    // boundary (x.5) by that much plus the rounding of sqrt and mul here (1.3e-7 relative) and in the
+    // reference (1.2e-7)
+    const float half = E < 0.01f * mm ? 0.51f : 1.01f;
+    const float dt = fmaf(E * prm.invlevel * half, rs, fmaf(tq, 3.0e-7f, 1.0e-6f));
+    if (fabsf(fabsf(tq - c) - 0.5f) > dt) return min(__float_as_int(cb) - 0x4B400000, prm.maxlevel);
     return -1;
 }
 
-template <bool PBC>
-__global__ void __launch_bounds__(kThreads, 3)
+// NT threads per CTA, CPS CTAs per SM (see cta_shape).
+template <bool PBC, int NT, int CPS>
+__global__ void __launch_bounds__(NT, CPS)
 mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_constant__ CUtensorMap tmapJ,
                   const MdmatParams prm) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int kThreads = NT, kWarps = NT / 32;
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int kpad = prm.kpad, fbmax = prm.fb;
     const int pstride = kpad * kTile;                 // floats between planes of one frame's tile
-    float* aI = reinterpret_cast<float*>(smem_raw);                       // [fb][4][64][kpad]
-    float* aJ = aI + (size_t)fbmax * kPlanesI * pstride;                  // [fb][3][kpad][64]
+    float* aI = reinterpret_cast<float*>(smem_raw);                       // [fb][3][64][kpad]
+    float* aJ = aI + (size_t)fbmax * kPlanesI * pstride;                  // [fb][4][64][kpad]
     float4* sphI = reinterpret_cast<float4*>(aJ + (size_t)fbmax * kPlanesJ * pstride);   // [fb][64]
     float4* sphJ = sphI + fbmax * kTile;
     float4* grpI = sphJ + fbmax * kTile;              // [64] sphere around the residue over the whole group
@@ -470,19 +491,16 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     int* cntI = reinterpret_cast<int*>(grpJ + kTile);
     int* cntJ = cntI + kTile;
     uint16_t* list = reinterpret_cast<uint16_t*>(cntJ + kTile);          // [kListCap]
-    uint16_t* slow = list + kListCap;                                     // [kSlowCap]
-    uint64_t* bar = reinterpret_cast<uint64_t*>(slow + kSlowCap);
-    int* counters = reinterpret_cast<int*>(bar + 1);   // [0] list [1] redo list [2] near [3] evals [4] survivors
+    uint64_t* bar = reinterpret_cast<uint64_t*>(list + kListCap);
+    int* counters = reinterpret_cast<int*>(bar + 1);   // [0] list [2] near [3] evals
     int* rowbase = counters + 6;                        // [64] element index of pair (row residue, residue 0) in a frame row
     int* origI = rowbase + kTile;                       // [64] residue at row position i / column position j of the tile
     int* origJ = origI + kTile;
     float* boxs = reinterpret_cast<float*>(origJ + kTile);   // [kMaxFB][6] box lengths of the group's frames and their reciprocals
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t blk = blockIdx.x;
-    const int64_t grp = blk / prm.ntiles;
-    const int t = (int)(blk - grp * prm.ntiles);
-    const int64_t f0 = grp * fbmax;                                  // first frame of the group
+    const int t = (int)blockIdx.x;                                   // tile
+    const int64_t f0 = (int64_t)blockIdx.y * fbmax;                  // first frame of the group
     const int nfb = (int)min((int64_t)fbmax, prm.nf - f0);
     int ti, tj;
     if (prm.symmetric) {
@@ -522,19 +540,18 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             const uint32_t bytes = (uint32_t)fbmax * (kPlanesI + kPlanesJ) * (uint32_t)pstride * 4u;
             mbar_expect_tx(bar, bytes);
             tma_load_4d(aI, &tmapI, bar, 0, gi0, 0, (int)f0);
-            tma_load_4d(aJ, &tmapJ, bar, gj0, 0, 0, (int)f0);
+            tma_load_4d(aJ, &tmapJ, bar, 0, gj0, 0, (int)f0);
         }
     } else {
         for (int g = 0; g < nfb; g++) {
             const float* src = prm.slots + (size_t)(f0 + g) * kPlanes * kpad * prm.nres_pad;
             for (int idx = tid; idx < kPlanesI * pstride; idx += kThreads) {
                 const int pl = idx / pstride, rk = idx - pl * pstride;   // rk = residue * kpad + k
-                aI[(size_t)g * kPlanesI * pstride + idx] =
-                    src[(size_t)(kPlanesJ + pl) * kpad * prm.nres_pad + (size_t)gi0 * kpad + rk];
+                aI[(size_t)g * kPlanesI * pstride + idx] = src[(size_t)pl * kpad * prm.nres_pad + (size_t)gi0 * kpad + rk];
             }
             for (int idx = tid; idx < kPlanesJ * pstride; idx += kThreads) {
-                const int r = idx & (kTile - 1), pk = idx >> 6;
-                aJ[(size_t)g * kPlanesJ * pstride + idx] = src[(size_t)pk * prm.nres_pad + gj0 + r];
+                const int pl = idx / pstride, rk = idx - pl * pstride;
+                aJ[(size_t)g * kPlanesJ * pstride + idx] = src[(size_t)pl * kpad * prm.nres_pad + (size_t)gj0 * kpad + rk];
             }
         }
     }
@@ -542,8 +559,8 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     // pruning runs once per group instead of once per frame.  In a periodic run the residue's centre in
     // frame g is its centre in the group's first frame plus the minimum image of the displacement, modulo
     // that frame's box, which is all the torus triangle inequality of the pruning test needs.
-    if (PBC && tid >= 2 * kTile && tid < 2 * kTile + nfb * 3) {
-        const int q = tid - 2 * kTile, g = q / 3, c = q % 3;
+    if (PBC && tid < nfb * 3) {
+        const int q = tid, g = q / 3, c = q % 3;
         const float L = prm.box[9 * (f0 + g) + 4 * c];
         boxs[6 * g + c] = L;
         boxs[6 * g + 3 + c] = L > 0.f ? 1.0f / L : 0.f;
@@ -592,7 +609,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     }
 
     // ---- fill: every pair of the tile starts at the "beyond trunc" level -------------------
-    {
+    if (!(prm.dbg & 2)) {
         // a quarter of a warp per row: 8 lanes x 8 levels (one 16-byte store) cover the 64 columns
         const int sub = lane >> 3, l8 = lane & 7;
         const uint32_t fillv = (uint32_t)maxlevel * 0x00010001u;
@@ -627,64 +644,59 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     auto process_list = [&]() {
         if (!tiles_ready) { mbar_wait(bar, 0); tiles_ready = true; }
         const int nent = counters[0];
-        const int nitems = nent * nfb;
-        int near = 0, evals = 0;
+        const int nitems = (prm.dbg & 4) ? 0 : nent * nfb;
+        const int swz = prm.swz ? 4 : 0;     // 32-byte swizzle: residues 4..7 of every eight have their halves exchanged
+        const bool k8 = kpad == 8;
         int gq = 0, qq = tid;      // frame-major walk over (frame, entry): a warp's lanes share the frame,
                                    // so their tile reads fall into different banks
-        for (int s = tid; s < nitems; s += kThreads, qq += kThreads) {
-            int e, g;
-            while (qq >= nent) { qq -= nent; gq++; }
-            g = gq; e = list[qq];
+        // whole warps walk the items together (the exact path below is taken by all 32 lanes)
+        for (int s0 = warp * 32; s0 < nitems; s0 += kThreads, qq += kThreads) {
+            const bool have = s0 + lane < nitems;
+            while (qq >= nent && gq < nfb - 1) { qq -= nent; gq++; }
+            const int g = gq;
+            const int e = have ? list[qq] : 0;
             const int i = e & 63, j = (e >> 6) & 63;
-            const int ci = cntI[i], cj = cntJ[j];
-            evals += ci * cj;
-            int level = -1;
-            if (!PBC || !(e & 0x1000))
-                level = fast_pair<PBC>(prm, aI + (size_t)g * kPlanesI * pstride + i * kpad, aJ + (size_t)g * kPlanesJ * pstride + j,
-                                       pstride, sphI[g * kTile + i], sphJ[g * kTile + j], ci, cj,
-                                       PBC ? boxs + 6 * g : nullptr);
-            if (level < 0) {
-                const int k = atom_add_shared(&counters[1], 1);
-                if (k < kSlowCap) {
-                    slow[k] = (uint16_t)((e & 0x1fff) | (g << 13));
-                    continue;
+            int level = maxlevel;
+            if (have) {
+                const int ci = cntI[i], cj = cntJ[j];
+                level = -1;
+                if (!PBC || !(e & 0x1000)) {
+                    const float* ri = aI + g * (kPlanesI * pstride) + i * kpad;
+                    const float* rj = aJ + g * (kPlanesJ * pstride) + j * kpad;
+                    if (k8)
+                        level = fast_pair<PBC, true>(prm, ri, rj, 8 * kTile, swz & i, swz & j, sphI[g * kTile + i],
+                                                     sphJ[g * kTile + j], ci, cj, PBC ? boxs + 6 * g : nullptr);
+                    else
+                        level = fast_pair<PBC, false>(prm, ri, rj, pstride, 0, 0, sphI[g * kTile + i],
+                                                      sphJ[g * kTile + j], ci, cj, PBC ? boxs + 6 * g : nullptr);
                 }
-                float Lx = 0.f, Ly = 0.f, Lz = 0.f;   // redo list full: take the exact path right here
+            }
+            // The pairs the expanded form could not certify are redone right here, one after the other, each
+            // by the whole warp with the reference's operation order (no list, no block barrier).
+            unsigned need = __ballot_sync(0xffffffffu, level < 0);
+            if (prm.dbg & 1) need = 0;
+            while (need) {
+                const int src = __ffs(need) - 1;
+                need &= need - 1;
+                const int es = __shfl_sync(0xffffffffu, e, src), gs = __shfl_sync(0xffffffffu, g, src);
+                const int is = es & 63, js = (es >> 6) & 63;
+                float Lx = 0.f, Ly = 0.f, Lz = 0.f;
                 if (PBC) {
-                    const float* b = prm.box + 9 * (f0 + g);
-                    Lx = b[0]; Ly = b[4]; Lz = b[8];
+                    // A pair whose spheres stay inside half a box and whose centres need no lattice shift has every
+                    // atom difference inside (-L/2, L/2): the minimum image leaves it alone, so it is not applied.
+                    const float4 a = sphI[gs * kTile + is], b = sphJ[gs * kTile + js];
+                    const float* bl = boxs + 6 * gs;
+                    const float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
+                    const bool image = (es & 0x1000) || nearest_image(dx, bl[0]) != dx || nearest_image(dy, bl[1]) != dy ||
+                                       nearest_image(dz, bl[2]) != dz;
+                    if (image) { Lx = bl[0]; Ly = bl[1]; Lz = bl[2]; }
                 }
-                level = exact_pair(prm, f0 + g, origI[i], origJ[j], Lx, Ly, Lz, near);
+                const int lv = exact_pair_warp(prm, f0 + gs, origI[is], origJ[js], Lx, Ly, Lz, lane, &counters[2]);
+                if (lane == src) level = lv;
             }
             if (level < maxlevel)
                 prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + origJ[j]] = (uint16_t)level;
         }
-        __syncthreads();
-        const int nslow = min(counters[1], kSlowCap);
-        for (int s = warp; s < nslow; s += kWarps) {      // one warp per pair on the exact path
-            const int e = slow[s];
-            const int i = e & 63, j = (e >> 6) & 63, g = e >> 13;
-            float Lx = 0.f, Ly = 0.f, Lz = 0.f;
-            if (PBC) {
-                // A pair whose spheres stay inside half a box and whose centres need no lattice shift has every
-                // atom difference inside (-L/2, L/2): the minimum image leaves it alone, so it is not applied.
-                const float4 a = sphI[g * kTile + i], b = sphJ[g * kTile + j];
-                const float* bl = boxs + 6 * g;
-                const float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
-                const bool image = (e & 0x1000) || nearest_image(dx, bl[0]) != dx || nearest_image(dy, bl[1]) != dy ||
-                                   nearest_image(dz, bl[2]) != dz;
-                if (image) { Lx = bl[0]; Ly = bl[1]; Lz = bl[2]; }
-            }
-            const int level = exact_pair_warp(prm, f0 + g, origI[i], origJ[j], Lx, Ly, Lz, lane, near);
-            if (lane == 0)
-                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + origJ[j]] = (uint16_t)level;
-        }
-        near = __reduce_add_sync(0xffffffffu, near);
-        evals = __reduce_add_sync(0xffffffffu, evals);
-        if (lane == 0 && near) atom_add_shared(&counters[2], near);
-        if (lane == 0 && evals) atom_add_shared(&counters[3], evals);
-        __syncthreads();
-        if (tid == 0) { counters[4] += nitems; counters[0] = 0; counters[1] = 0; }
         __syncthreads();
     };
 
@@ -709,7 +721,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         // sides; a sub-block's survivors go into the list as one contiguous run (one reservation), and the
         // 32 lanes that later take 32 consecutive entries run the same number of loop trips.
 #pragma unroll 1
-        for (int sb = warp; sb < 16; sb += kWarps) {
+        for (int sb = warp; sb < ((prm.dbg & 8) ? 0 : 16); sb += kWarps) {
             const int rb = (sb >> 2) * 16, cb = (sb & 3) * 16;
             const int j = cb + (lane & 15);
             const float4 sj = sJ[j];
@@ -717,6 +729,8 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             const int jres = origJ[j];
             const bool jok = jres >= j_beg && jres < j_end;
             unsigned keepbits = 0, genbits = 0, total = 0;
+            int evals = 0;               // atom pairs of the kept residue pairs (per frame)
+            const int cjn = cntJ[j];
             unsigned before[8];          // survivors of the sub-block ahead of this lane's k-th pair
 #pragma unroll
             for (int k = 0; k < 8; k++) {
@@ -755,6 +769,11 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 total += __popc(ball);
                 keepbits |= (keep ? 1u : 0u) << k;
                 genbits |= (general ? 1u : 0u) << k;
+                evals += keep ? cntI[i] * cjn : 0;
+            }
+            if (prm.counters) {
+                evals = __reduce_add_sync(0xffffffffu, evals);
+                if (lane == 0 && evals) atom_add_shared(&counters[3], evals);
             }
             if (total) {
                 int base = 0;
@@ -774,8 +793,8 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
 
     if (tid == 0 && prm.counters) {
         if (counters[2]) atomicAdd(&prm.counters[0], (unsigned long long)counters[2]);
-        if (counters[4]) atomicAdd(&prm.counters[1], (unsigned long long)counters[4]);
-        if (counters[3]) atomicAdd(&prm.counters[2], (unsigned long long)counters[3]);
+        if (counters[0]) atomicAdd(&prm.counters[1], (unsigned long long)(counters[0] * nfb));
+        if (counters[3]) atomicAdd(&prm.counters[2], (unsigned long long)counters[3] * (unsigned long long)nfb);
     }
 }
 
@@ -805,19 +824,37 @@ bool make_layout(int64_t nf, int nres, int max_res_atoms, Layout* L) {
 
 size_t mdmat_smem_bytes(int kpad, int fb) {
     size_t s = 0;
-    s += (size_t)fb * kPlanes * kpad * kTile * sizeof(float);   // atom tiles, both roles
+    s += (size_t)fb * (kPlanesI + kPlanesJ) * kpad * kTile * sizeof(float);   // atom tiles, rows and columns
     s += (size_t)(fb + 1) * 2 * kTile * sizeof(float4);         // per-frame and per-group spheres
     s += 2 * kTile * sizeof(int);                               // counts
-    s += (size_t)(kListCap + kSlowCap) * sizeof(uint16_t);      // survivor and redo lists
+    s += (size_t)kListCap * sizeof(uint16_t);                   // survivor list
     s += 8 + 6 * sizeof(int) + 3 * kTile * sizeof(int);         // mbarrier + counters + row bases + residue numbers
     s += kMaxFB * 6 * sizeof(float);                            // box lengths of the group's frames and reciprocals
     return (s + 15) & ~(size_t)15;
 }
 
-int frames_per_cta(int kpad) {
+// CTA shapes.  0: 256 threads x 2 CTAs per SM, up to 128 registers per thread and 112 KB of shared memory
+// (six frames per CTA at eight atoms per residue); 1: 256 threads x 3 CTAs per SM, 80 registers and 74 KB
+// (three frames).  The first is faster (18.0 against 20.0 ms per 12 500 frames of 1000 residues): the tile
+// kernel does not fit 80 registers without spilling in its item loop, and twice the frames per CTA halve
+// the set-up and pruning work per frame.
+struct CtaShape { int threads, per_sm; size_t budget; };
+inline CtaShape cta_shape(int cfg) {
+    if (cfg == 1) return CtaShape{256, 3, (size_t)74 * 1024};
+    return CtaShape{256, 2, (size_t)112 * 1024};
+}
+
+int frames_per_cta(int kpad, size_t budget) {
     int fb = kMaxFB;
-    while (fb > 1 && mdmat_smem_bytes(kpad, fb) > (size_t)kSmemBudget) fb--;
+    while (fb > 1 && mdmat_smem_bytes(kpad, fb) > budget) fb--;
     return fb;
+}
+
+// Largest residue (in atom slots) whose single-frame tiles still fit the shared memory of one CTA.
+int max_kpad() {
+    int k = 4;
+    while (mdmat_smem_bytes(k + 4, 1) <= (size_t)kSmemLimit) k += 4;
+    return k;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -835,6 +872,69 @@ EncodeTiledFn get_encode_fn() {
             fn = reinterpret_cast<EncodeTiledFn>(p);
     }
     return fn;
+}
+
+constexpr int kDefaultCfg = 0;        // CTA shape used unless CONAN_MDMAT_CFG says otherwise (see cta_shape)
+constexpr bool kDefaultSwz = true;
+
+// The two tensor maps of one launch.  Encoding costs a few microseconds of host time; a caller that
+// runs the same shapes on the same workspace call after call (a step loop) gets the previous pair back.
+struct TileMaps {
+    CUtensorMap I, J;
+    const void* base = nullptr;
+    int kpad = 0, nres_pad = 0, fb = 0, swz = 0;
+    int64_t nfl = 0;
+};
+
+const TileMaps* tile_maps(EncodeTiledFn encode, float* base, int kpad, int nres_pad, int64_t nfl, int fb, int swz) {
+    static thread_local TileMaps tm;
+    if (tm.base == base && tm.kpad == kpad && tm.nres_pad == nres_pad && tm.nfl == nfl && tm.fb == fb && tm.swz == swz)
+        return &tm;
+    const cuuint64_t plane_bytes = (cuuint64_t)kpad * nres_pad * 4;
+    cuuint64_t gdim[4] = {(cuuint64_t)kpad, (cuuint64_t)nres_pad, (cuuint64_t)kPlanes, (cuuint64_t)nfl};
+    cuuint64_t gstr[3] = {(cuuint64_t)kpad * 4, plane_bytes, plane_bytes * kPlanes};
+    cuuint32_t boxI[4] = {(cuuint32_t)kpad, (cuuint32_t)kTile, (cuuint32_t)kPlanesI, (cuuint32_t)fb};
+    cuuint32_t boxJ[4] = {(cuuint32_t)kpad, (cuuint32_t)kTile, (cuuint32_t)kPlanesJ, (cuuint32_t)fb};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    const CUtensorMapSwizzle sw = swz ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+    tm.base = nullptr;
+    CUresult cr = encode(&tm.I, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, boxI, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr == CUDA_SUCCESS)
+        cr = encode(&tm.J, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, boxJ, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) return nullptr;
+    tm.base = base; tm.kpad = kpad; tm.nres_pad = nres_pad; tm.nfl = nfl; tm.fb = fb; tm.swz = swz;
+    return &tm;
+}
+
+// Once per device: raise the dynamic shared-memory limit of every tile-kernel instantiation and make the
+// runtime load all kernels of this file, so that later calls (the allocation-free entry point in
+// particular) neither load code nor change function attributes inside a caller's step loop.
+constexpr int kMaxDevices = 64;
+bool g_device_ready[kMaxDevices] = {false};
+std::mutex g_device_mutex;
+
+int device_setup() {
+    int dev = -1;
+    CONAN_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices)
+        return conan::fail(CONAN_ERR_SIZE, "conan_mdmat_frames: device ordinal %d not supported (max %d)", dev, kMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_device_mutex);
+    if (g_device_ready[dev]) return CONAN_OK;
+    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<false, 256, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<true, 256, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<false, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<true, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    cudaFuncAttributes fa;
+    CONAN_CUDA_TRY(cudaFuncGetAttributes(&fa, block_perm_kernel));
+    CONAN_CUDA_TRY(cudaFuncGetAttributes(&fa, prep_slots_kernel<8>));
+    CONAN_CUDA_TRY(cudaFuncGetAttributes(&fa, prep_slots_kernel<16>));
+    CONAN_CUDA_TRY(cudaFuncGetAttributes(&fa, prep_slots_kernel<0>));
+    g_device_ready[dev] = true;
+    return CONAN_OK;
 }
 
 }  // namespace
@@ -885,8 +985,9 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
                            x0, xres, y0, yres, nres);
     Layout L;
     make_layout(nf, nres, max_atoms, &L);
-    if (L.kpad > kMaxKpad)
-        return conan::fail(CONAN_ERR_SIZE, "conan_mdmat_frames: a residue has %d atoms; the limit is %d", max_atoms, kMaxKpad);
+    if (L.kpad > max_kpad())
+        return conan::fail(CONAN_ERR_SIZE, "conan_mdmat_frames: a residue has %d atoms; the limit is %d (the tiles of "
+                           "one frame must fit %d KB of shared memory)", max_atoms, max_kpad(), kSmemLimit / 1024);
     if (work_bytes < L.total)
         return conan::fail(CONAN_ERR_SIZE, "conan_mdmat_frames: workspace %zu bytes, need %zu", work_bytes, L.total);
     if ((reinterpret_cast<uintptr_t>(d_work) & 255) != 0)
@@ -921,11 +1022,18 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
 
     EncodeTiledFn encode = get_encode_fn();
     if (!encode) return conan::fail(CONAN_ERR_CUDA, "conan_mdmat_frames: cuTensorMapEncodeTiled unavailable");
+    int rc = device_setup();
+    if (rc != CONAN_OK) return rc;
 
-    const int fb = frames_per_cta(L.kpad);
+    int cfg = kDefaultCfg;
+    {
+        const char* e = getenv("CONAN_MDMAT_CFG");
+        if (e && (e[0] == '0' || e[0] == '1')) cfg = e[0] - '0';
+    }
+    CtaShape shape = cta_shape(cfg);
+    if (mdmat_smem_bytes(L.kpad, 1) > shape.budget) shape.budget = (size_t)kSmemLimit;   // large residues: one CTA per SM
+    const int fb = frames_per_cta(L.kpad, shape.budget);
     const size_t smem = mdmat_smem_bytes(L.kpad, fb);
-    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CONAN_CUDA_TRY(cudaFuncSetAttribute(mdmat_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 
     MdmatParams prm;
     prm.cnt = d_cnt; prm.res_start = d_res_start; prm.perm = d_perm; prm.counters = d_counters;
@@ -942,6 +1050,13 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
     {
         const char* e = getenv("CONAN_MDMAT_NO_TMA");
         prm.use_tma = (e && e[0] == '1') ? 0 : 1;
+        // With eight slots a residue's record is 32 bytes per plane and eight consecutive residues would
+        // meet in four of the eight 16-byte bank groups; the 32-byte swizzle spreads them over all eight.
+        const char* d = getenv("CONAN_MDMAT_DEBUG");
+        prm.dbg = d ? atoi(d) : 0;
+        const char* z = getenv("CONAN_MDMAT_SWZ");
+        const bool want = z ? z[0] == '1' : kDefaultSwz;
+        prm.swz = (want && prm.use_tma && L.kpad == 8) ? 1 : 0;
     }
     const int64_t P = symmetric ? (int64_t)nres * (nres - 1) / 2 : (int64_t)xres * yres;
     if (P == 0) return CONAN_OK;
@@ -951,33 +1066,15 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
         return conan::fail(CONAN_ERR_ARG, "conan_mdmat_frames: levels_stride=%lld < P=%lld", (long long)levels_stride, (long long)P);
     prm.stride = levels_stride;
 
-    // Frames per launch: the TMA frame coordinate is an int and the grid is 1-D.
-    const int64_t max_blocks = 1ll << 30;
-    int64_t frames_per_launch = (max_blocks / prm.ntiles) * fb;
-    if (frames_per_launch < fb) frames_per_launch = fb;
+    // Frames per launch: the grid is (tiles, frame groups) and its second dimension ends at 65535.
+    const int64_t frames_per_launch = (int64_t)65535 * fb;
     for (int64_t fbase = 0; fbase < nf; fbase += frames_per_launch) {
         const int64_t nfl = (nf - fbase < frames_per_launch) ? nf - fbase : frames_per_launch;
-        // The tensor maps cover only this launch's frames, so coordinate 3 stays small.
-        CUtensorMap tmapI, tmapJ;
-        // column role: [frame][3 planes][kpad][residue]; row role (behind it in every frame): [4 planes][residue][kpad]
-        const cuuint64_t frame_bytes = (cuuint64_t)kPlanes * L.kpad * L.nres_pad * 4;
-        cuuint64_t gdimJ[4] = {(cuuint64_t)L.nres_pad, (cuuint64_t)L.kpad, (cuuint64_t)kPlanesJ, (cuuint64_t)nfl};
-        cuuint64_t gstrJ[3] = {(cuuint64_t)L.nres_pad * 4, (cuuint64_t)L.kpad * L.nres_pad * 4, frame_bytes};
-        cuuint64_t gdimI[4] = {(cuuint64_t)L.kpad, (cuuint64_t)L.nres_pad, (cuuint64_t)kPlanesI, (cuuint64_t)nfl};
-        cuuint64_t gstrI[3] = {(cuuint64_t)L.kpad * 4, (cuuint64_t)L.kpad * L.nres_pad * 4, frame_bytes};
-        cuuint32_t boxI[4] = {(cuuint32_t)L.kpad, (cuuint32_t)kTile, (cuuint32_t)kPlanesI, (cuuint32_t)fb};
-        cuuint32_t boxJ[4] = {(cuuint32_t)kTile, (cuuint32_t)L.kpad, (cuuint32_t)kPlanesJ, (cuuint32_t)fb};
-        cuuint32_t estr[4] = {1, 1, 1, 1};
+        // The tensor maps cover only this launch's frames, so coordinate 3 stays small.  Both describe the
+        // same tensor [frame][4 planes][residue][kpad]; the row tile takes three planes, the column tile four.
         float* base = d_slots + (size_t)fbase * kPlanes * L.kpad * L.nres_pad;
-        CUresult cr = encode(&tmapI, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base + (size_t)kPlanesJ * L.kpad * L.nres_pad, gdimI,
-                             gstrI, boxI, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (cr == CUDA_SUCCESS)
-            cr = encode(&tmapJ, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdimJ, gstrJ, boxJ, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (cr != CUDA_SUCCESS)
-            return conan::fail(CONAN_ERR_CUDA, "conan_mdmat_frames: cuTensorMapEncodeTiled failed (%d)", (int)cr);
+        const TileMaps* maps = tile_maps(encode, base, L.kpad, L.nres_pad, nfl, fb, prm.swz);
+        if (!maps) return conan::fail(CONAN_ERR_CUDA, "conan_mdmat_frames: cuTensorMapEncodeTiled failed");
         MdmatParams p2 = prm;
         // frame indices inside the kernel are relative to this launch's base pointers
         p2.sph = d_sph + (size_t)fbase * L.nres_pad;
@@ -987,8 +1084,14 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
         p2.slots = base;
         p2.nf = nfl;
         const int64_t ngroups = (nfl + fb - 1) / fb;
-        if (prm.pbc) mdmat_tile_kernel<true><<<(unsigned)(ngroups * prm.ntiles), kThreads, smem, stream>>>(tmapI, tmapJ, p2);
-        else mdmat_tile_kernel<false><<<(unsigned)(ngroups * prm.ntiles), kThreads, smem, stream>>>(tmapI, tmapJ, p2);
+        const dim3 grid((unsigned)prm.ntiles, (unsigned)ngroups);
+        if (shape.per_sm == 2) {
+            if (prm.pbc) mdmat_tile_kernel<true, 256, 2><<<grid, 256, smem, stream>>>(maps->I, maps->J, p2);
+            else mdmat_tile_kernel<false, 256, 2><<<grid, 256, smem, stream>>>(maps->I, maps->J, p2);
+        } else {
+            if (prm.pbc) mdmat_tile_kernel<true, 256, 3><<<grid, 256, smem, stream>>>(maps->I, maps->J, p2);
+            else mdmat_tile_kernel<false, 256, 3><<<grid, 256, smem, stream>>>(maps->I, maps->J, p2);
+        }
         CONAN_CUDA_TRY(cudaGetLastError());
     }
     return CONAN_OK;
@@ -1007,7 +1110,6 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
 static __device__ __align__(256) unsigned char g_mdmat_static_scratch[CONAN_MDMAT_STATIC_SCRATCH_BYTES];
 
 namespace {
-constexpr int kMaxDevices = 64;
 void* g_static_scratch_ptr[kMaxDevices] = {nullptr};
 std::mutex g_static_scratch_mutex;
 }  // namespace

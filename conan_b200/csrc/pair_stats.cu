@@ -453,11 +453,12 @@ int check_common(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, in
                  int32_t lo_cnt, int32_t* hi_first, int32_t equal_cut, const char* who) {
     if (!d_levels) return conan::fail(CONAN_ERR_ARG, "%s: null level stack", who);
     if (nf <= 0 || P <= 0) return conan::fail(CONAN_ERR_ARG, "%s: nf=%lld P=%lld", who, (long long)nf, (long long)P);
-    if (levels_stride < P || levels_stride % kVec != 0)
-        return conan::fail(CONAN_ERR_ARG, "%s: levels_stride=%lld must be >= P and a multiple of %d", who,
-                           (long long)levels_stride, kVec);
-    if ((reinterpret_cast<uintptr_t>(d_levels) & 7) != 0)
-        return conan::fail(CONAN_ERR_ARG, "%s: level rows must be 8-byte aligned", who);
+    // rows are streamed with cp.async.bulk: 16-byte aligned addresses and byte counts
+    if (levels_stride < P || levels_stride % 8 != 0)
+        return conan::fail(CONAN_ERR_ARG, "%s: levels_stride=%lld must be >= P and a multiple of 8", who,
+                           (long long)levels_stride);
+    if ((reinterpret_cast<uintptr_t>(d_levels) & 15) != 0)
+        return conan::fail(CONAN_ERR_ARG, "%s: level rows must be 16-byte aligned", who);
     if (nlevels < 2 || nlevels > 7744)
         return conan::fail(CONAN_ERR_SIZE, "%s: nlevels=%d outside [2, 7744] (the xpm two-character limit)", who, nlevels);
     if (lo_cnt < 0 || *hi_first < 0 || lo_cnt > nlevels || *hi_first > nlevels)

@@ -335,8 +335,11 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     triclinic = np.abs(boxes - boxes * np.eye(3)[None]).max() > 1e-6
     use_pbc = bool(pbc) and boxes[:, [0, 1, 2], [0, 1, 2]].min() > 0
     if use_pbc and triclinic:
-        print("Triclinic boxes are not supported by the minimum-image code; distances are computed without PBC.")
-        use_pbc = False
+        # gmx mdmat would search the triclinic shift vectors; carrying on without images would give
+        # different distances for every pair split across a box face, so stop instead.
+        print("The box of %s is triclinic; only rectangular boxes have a minimum-image path here." % traj)
+        print("Make the molecules whole and rerun with 'PBC no', or convert the trajectory to a rectangular box.")
+        sys.exit()
     nres_all = len(res_start) - 1
     if block is not None and (block[0] < 0 or block[2] < 0 or block[0] + block[1] > nres_all or block[2] + block[3] > nres_all):
         print("The X / Y residue ranges do not fit the %d residues of the index group; computing all pairs." % nres_all)

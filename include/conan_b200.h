@@ -193,7 +193,8 @@ typedef struct conan_frame_stats_out {
 size_t conan_pair_stats_workspace_bytes(int64_t nf, int64_t P);
 
 /*
- * d_levels  [nf][levels_stride] uint16, 8-byte aligned, levels_stride a multiple of 4.
+ * d_levels  [nf][levels_stride] uint16, 16-byte aligned, levels_stride a multiple of 8 (rows are
+ *           streamed with 16-byte bulk copies).
  *           frame0 = global index of the first frame of this call (frame numbers written to
  *           first_f/last_f are global).
  * lo_cnt / hi_first: TRUNC_INTER / TRUNC_INTER_HIGH in level space: r < trunc_inter <=> k < lo_cnt,
