@@ -158,7 +158,8 @@ __device__ __forceinline__ void close_window(unsigned h, int n, unsigned carry, 
 struct FramePart {
     unsigned cnt;        // (native << 16) | total pairs on
     unsigned sp_lo, s0_lo;
-    unsigned hi;         // WIDE only: (sp_hi << 16) | s0_hi carry words of the split sums
+    unsigned sp_hi;      // WIDE only: carry word of the split ssd_prev sum (its ssd_first twin sits in s_hi0:
+                         // two 16-bit fields in one word overflow above ~5800 levels)
 };
 
 // One frame for the thread's four pairs.  `wx`, `wy` are the two packed level words.
@@ -166,7 +167,8 @@ template <bool WIDE>
 __device__ __forceinline__ void frame_step(unsigned wx, unsigned wy, unsigned c_lo, unsigned c_hi, unsigned valid_y,
                                            unsigned native_y, unsigned& on_x, unsigned& on_y, unsigned (&hist)[kVec],
                                            unsigned (&a1)[kVec], unsigned (&a2)[kVec], unsigned (&kp)[kVec],
-                                           const unsigned (&k0)[kVec], FramePart* slot, bool lane0, int one) {
+                                           const unsigned (&k0)[kVec], FramePart* slot, unsigned* slot_hi0, bool lane0,
+                                           int one) {
     // hysteresis for four pairs: on = below_lo | (on & ~above_hi), verdicts in bits 15 / 31
     const unsigned ge_lo_x = wx + c_lo, ge_hi_x = wx + c_hi;
     const unsigned ge_lo_y = wy + c_lo, ge_hi_y = wy + c_hi;
@@ -192,21 +194,27 @@ __device__ __forceinline__ void frame_step(unsigned wx, unsigned wy, unsigned c_
     const unsigned flags = __byte_perm(on_x, on_y, 0x7531) & valid_y;
     FramePart part;
     part.cnt = __reduce_add_sync(0xffffffffu, (__popc(flags & native_y) << 16) + __popc(flags));
+    unsigned s0_hi = 0;
     if (!WIDE) {
         part.sp_lo = __reduce_add_sync(0xffffffffu, sp);
         part.s0_lo = __reduce_add_sync(0xffffffffu, s0);
-        part.hi = 0;
-    } else {
+        part.sp_hi = 0;
+    } else {   // 128 squares of up to 7743^2 do not fit 32 bits: 16-bit halves, every sum in a word of its own
         part.sp_lo = __reduce_add_sync(0xffffffffu, sp & 0xffffu);
         part.s0_lo = __reduce_add_sync(0xffffffffu, s0 & 0xffffu);
-        part.hi = (__reduce_add_sync(0xffffffffu, sp >> 16) << 16) | __reduce_add_sync(0xffffffffu, s0 >> 16);
+        part.sp_hi = __reduce_add_sync(0xffffffffu, sp >> 16);
+        s0_hi = __reduce_add_sync(0xffffffffu, s0 >> 16);
     }
-    if (lane0) *reinterpret_cast<uint4*>(slot) = make_uint4(part.cnt, part.sp_lo, part.s0_lo, part.hi);
+    if (lane0) {
+        *reinterpret_cast<uint4*>(slot) = make_uint4(part.cnt, part.sp_lo, part.s0_lo, part.sp_hi);
+        if (WIDE) *slot_hi0 = s0_hi;
+    }
 }
 
 template <bool MASKED, bool WIDE>
 __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s_part)[kThreads / 32][kWin],
-                                           const uint16_t* s_rows, uint64_t* full_bar, uint64_t* empty_bar) {
+                                           unsigned (*s_hi0)[kThreads / 32][kWin], const uint16_t* s_rows,
+                                           uint64_t* full_bar, uint64_t* empty_bar) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool lane0 = lane == 0;
     const int64_t p0 = ((int64_t)blockIdx.x * kThreads + tid) * kVec;
@@ -273,6 +281,7 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
     for (int64_t fb = fbeg; fb < fend; fb += kWin, buf ^= 1) {
         const int nblk = (int)min((int64_t)kWin, fend - fb);
         FramePart* slots = &s_part[buf][warp][0];
+        unsigned* slots_hi0 = &s_hi0[buf][warp][0];
 #pragma unroll 1
         for (int u0 = 0; u0 < nblk; u0 += kStageFrames, it++) {
             const int slot = it % kStagesS;
@@ -284,14 +293,14 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
                     uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
                     if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
                     frame_step<WIDE>(w.x, w.y, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
-                                     slots + u0 + u, lane0, prm.one);
+                                     slots + u0 + u, slots_hi0 + u0 + u, lane0, prm.one);
                 }
             } else {   // the last, partial stage of the call
                 for (int u = 0; u < nblk - u0; u++) {
                     uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
                     if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
                     frame_step<WIDE>(w.x, w.y, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
-                                     slots + u0 + u, lane0, prm.one);
+                                     slots + u0 + u, slots_hi0 + u0 + u, lane0, prm.one);
                 }
             }
             __syncwarp();
@@ -318,8 +327,9 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
             for (int w8 = 0; w8 < kThreads / 32; w8++) {
                 const FramePart fp = s_part[buf][w8][tid];
                 cnt += fp.cnt;
-                vp += (unsigned long long)fp.sp_lo + ((unsigned long long)(fp.hi >> 16) << 16);
-                v0 += (unsigned long long)fp.s0_lo + ((unsigned long long)(fp.hi & 0xffffu) << 16);
+                vp += (unsigned long long)fp.sp_lo + ((unsigned long long)fp.sp_hi << 16);
+                v0 += (unsigned long long)fp.s0_lo;
+                if (WIDE) v0 += (unsigned long long)s_hi0[buf][w8][tid] << 16;
             }
             const int64_t f = fb + tid;
             const int nat = (int)(cnt >> 16), tot = (int)(cnt & 0xffffu);
@@ -351,6 +361,7 @@ template <bool WIDE>
 __global__ void __launch_bounds__(kThreads + 32, 2) pair_stats_kernel(const StatsParams prm) {
     extern __shared__ __align__(128) unsigned char s_dyn[];    // [kStagesS][kStageFrames][1024] levels
     __shared__ __align__(16) FramePart s_part[2][kThreads / 32][kWin];   // per-warp, per-frame partial sums
+    __shared__ unsigned s_hi0[2][kThreads / 32][kWin];                   // WIDE only: carry words of the ssd_first sums
     __shared__ __align__(8) uint64_t full_bar[kStagesS], empty_bar[kStagesS];
     uint16_t* s_rows = reinterpret_cast<uint16_t*>(s_dyn);
     if (threadIdx.x == 0) {
@@ -381,8 +392,8 @@ __global__ void __launch_bounds__(kThreads + 32, 2) pair_stats_kernel(const Stat
     }
     // only the last pair tile can contain padding columns
     const bool tail = ((int64_t)(blockIdx.x + 1) * kPairsPerCta > prm.P);
-    if (tail) stats_body<true, WIDE>(prm, s_part, s_rows, full_bar, empty_bar);
-    else stats_body<false, WIDE>(prm, s_part, s_rows, full_bar, empty_bar);
+    if (tail) stats_body<true, WIDE>(prm, s_part, s_hi0, s_rows, full_bar, empty_bar);
+    else stats_body<false, WIDE>(prm, s_part, s_hi0, s_rows, full_bar, empty_bar);
 }
 
 struct CombineParams {

@@ -42,11 +42,12 @@ def _globule(rng, nres, density=7.0, bond=0.38, min_dist=0.30):
     return pos, R
 
 
-def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtype=np.float32):
+def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtype=np.float32, closer=0.0):
     """Returns (xyz [nframes, natoms, 3] float32 nm, res_start [nres+1] int32, box_length nm).
 
     two_chain=(nx, ny): two globules of nx and ny residues whose separation follows an OU process
-    around 1.5 nm surface distance (the asymmetric interface configuration)."""
+    around 1.5 nm surface distance (the asymmetric interface configuration); closer (nm) moves the second
+    globule towards the first, for small systems that should share more than a handful of contacts."""
     rng = np.random.default_rng(seed)
     if two_chain is None:
         centres, R = _globule(rng, nres)
@@ -56,7 +57,7 @@ def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtyp
         assert nx + ny == nres
         c1, R1 = _globule(rng, nx)
         c2, R2 = _globule(rng, ny)
-        centres = np.concatenate([c1, c2 + np.array([R1 + R2 + 0.3, 0.0, 0.0])])
+        centres = np.concatenate([c1, c2 + np.array([R1 + R2 + 0.3 - closer, 0.0, 0.0])])
         R = R1 + R2 + 1.0
         shift = (nx, ny)
     offsets = rng.normal(0.0, 0.15, size=(nres, atoms_per_res, 3))
@@ -84,10 +85,13 @@ def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtyp
             sep[f] = v
         cen[:, nx:, 0] += sep[:, None]
     L = float(4.0 * R + 4.0)
-    xyz = (cen[:, :, None, :] + offsets[None, :, :, :]).reshape(nframes, nres * atoms_per_res, 3) + L / 2.0
-    xyz = np.round(xyz * 1000.0) / 1000.0
+    # assembled in blocks of frames: the float64 intermediate of a 12 500-frame shard would be 2.4 GB
+    xyz = np.empty((nframes, nres * atoms_per_res, 3), dtype=dtype)
+    for f0 in range(0, nframes, 1024):
+        blk = (cen[f0:f0 + 1024, :, None, :] + offsets[None, :, :, :]).reshape(-1, nres * atoms_per_res, 3) + L / 2.0
+        xyz[f0:f0 + 1024] = np.round(blk * 1000.0) / 1000.0
     res_start = (np.arange(nres + 1) * atoms_per_res).astype(np.int32)
-    return xyz.astype(dtype), res_start, L
+    return xyz, res_start, L
 
 
 def make_protein_like(nres, nframes, seed=7):

@@ -13,6 +13,14 @@ Fixtures written
   case_*.npz            inputs and outputs of the UNMODIFIED reference run here (oracle/ref_runner.py)
                         on synthetic level stacks that exercise hysteresis, observables, PCA,
                         frame clustering and the asymmetric mode
+  ubi_pull_500ps.xtc    the reference's ubiquitin unfolding trajectory (applications/1_ubi_unfold, 472 frames
+  ubi.pdb               of 1231 atoms, 2 MB) and its structure file: BASELINE.json configs[1]
+  case_ubi.npz          outputs of the unmodified reference on that trajectory with the keywords of
+                        applications/1_ubi_unfold/fine.inp plus a STAGES file; its dmf.xpm comes from the CPU
+                        restatement of gmx mdmat (oracle/), since gmx itself is unavailable
+  case_c5.npz           the same for a small two-chain interface system (50 x 100 residues, 200 frames) in the
+                        asymmetric mode with K_TRAJ_CLUSTERS 2-5: BASELINE.json configs[4] scaled to what the
+                        reference finishes in a minute
 """
 import os
 import shutil
@@ -105,7 +113,7 @@ def synthetic_levels(seed, nf, nres, nlevels, lo, hi):
     return full
 
 
-def run_case(name, full, times, trunc, nlevels, keywords, obs=None, extra_files=None):
+def run_case(name, full, times, trunc, nlevels, keywords, obs=None, extra_files=None, store_levels=True, keep=None):
     work = tempfile.mkdtemp(prefix="conan_golden_")
     with open(os.path.join(work, "dmf.xpm"), "w") as f:
         xpm.write_xpm(f, full, times, trunc, nlevels)
@@ -123,12 +131,20 @@ def run_case(name, full, times, trunc, nlevels, keywords, obs=None, extra_files=
         with open(os.path.join(work, fname), "w") as f:
             f.write(content)
     g = ref_runner.run_reference(work, text)
-    out = {"in/levels_full": full, "in/times": np.asarray(times, np.float64), "in/trunc": np.float64(trunc),
+    out = {"in/times": np.asarray(times, np.float64), "in/trunc": np.float64(trunc),
            "in/nlevels": np.int64(nlevels), "in/keywords": np.array(text)}
+    if store_levels:
+        out["in/levels_full"] = full
+    else:   # large stacks are recomputed by the test from the trajectory; a digest and three frames pin them
+        import hashlib
+        out["in/levels_sha256"] = np.array(hashlib.sha256(np.ascontiguousarray(full).tobytes()).hexdigest())
+        out["in/levels_sample"] = full[[0, len(full) // 2, len(full) - 1]]
     if obs is not None:
         out["in/obs"] = obs
     for k, v in parse_tree(work).items():
         if k.startswith("input/") or k.startswith("oldpca/") or k == "ref.inp" or k == "obs.dat":
+            continue
+        if keep is not None and not keep(k):
             continue
         out["file/" + k] = v
     out["ret/vectors"] = np.asarray(g["vectors"])
@@ -141,10 +157,56 @@ def run_case(name, full, times, trunc, nlevels, keywords, obs=None, extra_files=
     print("case_%s.npz:" % name, len(out), "arrays;", "pairs", len(g["pairs_list"]))
 
 
+UBI_STAGES = '#Three stages of the pulling run\n0 60000 "folded"\n60000 150000 "unfolding"\n150000 235500 "extended"\n'
+
+
+def ubi_case():
+    """BASELINE.json configs[1]: applications/1_ubi_unfold with the keywords of fine.inp (:3-8, :13) minus
+    GNUS_PATH / COORD_PDB / DOMAINS, plus STAGES (conan.py:798-805, :961-990)."""
+    from oracle import oracle
+    app = os.path.join(REF, "applications/1_ubi_unfold")
+    shutil.copyfile(os.path.join(app, "pull_500ps.xtc"), os.path.join(OUT, "ubi_pull_500ps.xtc"))
+    shutil.copyfile(os.path.join(app, "ubi.pdb"), os.path.join(OUT, "ubi.pdb"))
+    top = topology.read_topology(os.path.join(OUT, "ubi.pdb"))
+    x = XtcFile(os.path.join(OUT, "ubi_pull_500ps.xtc"))
+    sel = top.default_groups()[2][1]                       # Protein-H, what the reference's tests pick
+    res_start = top.residue_runs(sel)
+    xyz = x.decode()
+    full = oracle.mdmat_levels(xyz, x.boxes, sel, res_start, 1.0, 1001, 1)
+    print("ubiquitin: %d frames, %d atoms, %d selected, %d residues" % (len(xyz), xyz.shape[1], len(sel), len(res_start) - 1))
+    sample = {"00000", "00235", "00471"}
+    run_case("ubi", full, x.times, 1.0, 1001,
+             "DT 500\nTRUNC_INTER 0.5\nTRUNC_DR 1.0\nDR_MODE init\nK_TRAJ_CLUSTERS 1-5\nSTAGES stages.txt\n",
+             extra_files={"stages.txt": UBI_STAGES}, store_levels=False,
+             keep=lambda k: not k.startswith("matrices/") or k.split("/")[1][:5] in sample or k.split("/")[1].startswith("stage_"))
+
+
+def c5_case():
+    """BASELINE.json configs[4] at a size the reference finishes in a minute: two chains of 50 and 100
+    residues, 200 frames, START_X / NRES_X / START_Y / NRES_Y as SURVEY section 8(d) writes them."""
+    import hashlib
+    from conan_b200 import synth
+    from oracle import oracle
+    nx, ny, nf = 50, 100, 200
+    xyz, res_start, _ = synth.make_trajectory(nx + ny, nf, 8, seed=5, two_chain=(nx, ny), closer=0.7)
+    full = oracle.mdmat_levels(xyz, None, np.arange(xyz.shape[1]), res_start, 1.0, 1001, 0)
+    run_case("c5", full, np.arange(nf) * 100, 1.0, 1001,
+             "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nSTART_X 1\nNRES_X %d\nNTERM_X 1\nSTART_Y %d\nNRES_Y %d\nNTERM_Y %d\n"
+             "MATRICES no\nK_TRAJ_CLUSTERS 2-5\n" % (nx, nx + 1, ny, nx + 1), store_levels=False)
+    c = dict(np.load(os.path.join(OUT, "case_c5.npz")))
+    c["in/xyz_sha256"] = np.array(hashlib.sha256(np.ascontiguousarray(xyz).tobytes()).hexdigest())
+    c["in/synth"] = np.array([nx, ny, nf, 8, 5, 0.7])
+    np.savez_compressed(os.path.join(OUT, "case_c5.npz"), **c)
+
+
 def main():
     if not ref_runner.available():
         sys.exit("needs /root/reference")
     only = sys.argv[1] if len(sys.argv) > 1 else None
+    if only == "ubi":
+        return ubi_case()
+    if only == "c5":
+        return c5_case()
     if not only:
         peptide_fixture()
         reference_goldens()
@@ -182,6 +244,8 @@ def main():
                  "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nMATRICES no\nPCA_READ oldpca\n", extra_files=pcs)
     if only:
         return
+    ubi_case()
+    c5_case()
     # finer legend: 1001 levels, trunc 1.5 (dx = 0.0015, not a multiple of 1e-4)
     full2 = synthetic_levels(12, 30, 9, 1001, 0.5, 0.6)
     run_case("fine", full2, np.arange(30) * 500 + 1000, 1.5, 1001,

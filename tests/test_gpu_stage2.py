@@ -92,6 +92,48 @@ def test_frame_shards_compose(lib, orc):
         assert np.array_equal(np.concatenate([ha[k], hb[k]]), want[k]), k
 
 
+def test_full_range_jumps_at_the_level_limit(lib, orc):
+    """7744 levels, every pair of a warp jumping across the whole range between frames: the split per-frame
+    sums (16-bit halves of up to 128 x 7743^2) must not spill into each other."""
+    from conan_b200 import stage2
+    nf, P, nlevels = 70, 1024 + 128, 7744
+    levels = np.zeros((nf, P), np.uint16)
+    levels[1::2] = nlevels - 1                       # frame 0 at level 0, then alternating ends of the range
+    levels[5, ::3] = 4000
+    want = orc.pair_stats(levels, 3000, 5000, 0)
+    got = stage2.pair_stats(_device_stack(levels), P, nlevels, 3000, 5000, 0).host()
+    _check(got, want)
+    assert int(got["ssd_first"][1]) == P * (nlevels - 1) ** 2
+
+
+@pytest.mark.parametrize("fill", ["last", "none"])
+def test_stack_entirely_on_or_off_the_last_level(lib, orc, fill):
+    """A stack that is 100 % "beyond trunc" and one that never touches the last level."""
+    from conan_b200 import stage2
+    rng = np.random.default_rng(11)
+    nf, P, nlevels = 150, 2000, 1001
+    if fill == "last":
+        levels = np.full((nf, P), nlevels - 1, np.uint16)
+    else:
+        levels = rng.integers(0, nlevels - 1, size=(nf, P)).astype(np.uint16)
+    want = orc.pair_stats(levels, 500, 601, 0)
+    got = stage2.pair_stats(_device_stack(levels), P, nlevels, 500, 601, 0).host()
+    _check(got, want)
+
+
+def test_misaligned_stack_is_rejected(lib):
+    """Rows are streamed with 16-byte bulk copies: a pitch of 4 mod 8 or an 8-byte aligned base is an error."""
+    import torch
+    from conan_b200 import stage2
+    from conan_b200._lib import ConanError
+    d = torch.zeros((4, 12), dtype=torch.uint16, device="cuda")
+    with pytest.raises(ConanError):
+        stage2.pair_stats(d, 10, 101, 50, 60, 0)
+    e = torch.zeros(4 * 64 + 4, dtype=torch.uint16, device="cuda")[4:].view(4, 64)
+    with pytest.raises(ConanError):
+        stage2.pair_stats(e, 10, 101, 50, 60, 0)
+
+
 def test_bad_arguments_are_errors(lib):
     import torch
     from conan_b200 import stage2
