@@ -13,10 +13,16 @@ merged with an NCCL all-reduce and the hysteresis state carried across shards.
 
 One JSON line is printed by rank 0 (see the repository's bench contract):
   value      whole-job pair-frames/s with the coordinates already resident in HBM
-  e2e        same metric through the C-ABI with HOST (pinned) coordinates: H2D of every frame
-             batch and D2H of the per-pair / per-frame results inside the timed region
+  e2e        same metric through the C-ABI from HOST memory, starting where the reference starts: the shard's
+             compressed .xtc bytes (pinned) are copied H2D batch by batch, decoded on the GPU
+             (conan_xtc_decode_device), and the per-pair / per-frame results are read back, all inside
+             the timed region
   roofline   the dominant kernel (mdmat_tile_kernel), timed alone with CUDA events
   cpu_baseline  the CPU oracle (a port: gmx is unavailable) on a bounded sample, one thread
+  c2, c5     BASELINE.json configs[1] (the reference's ubiquitin unfolding run, whole) and configs[4]
+             (200 x 400 residue interface, 20 000 frames, frame-frame distances), rank 0 only
+On more than one GPU the frame shards are consecutive ranges of ONE trajectory, and before anything is
+timed tools/sharded_check.py compares the sharded stage 2 / stage 3 with a single-GPU run ("sharded_check").
 """
 import argparse
 import ctypes
@@ -37,6 +43,10 @@ ATOMS_PER_RES = 8
 FRAMES_PER_GPU = 12500
 TRUNC, NLEVELS = 1.0, 1001
 TRUNC_INTER, TRUNC_INTER_HIGH = 0.5, 0.6
+# the reference's own stage 2 (read_process_frames, one thread), measured in the survey container where
+# /root/reference exists; the box that runs this file has no reference tree
+REFERENCE_CONAN_PY = {"us_per_pair_frame": 32.0, "pair_frames_per_s": 1.0e6 / 32.0, "threads": 1,
+                      "source": "BASELINE.md section 3: read_process_frames on 330 frames x 378 pairs, 3.96 s"}
 METRIC = "residue-pair-frames/s (min-dist + contact stats)"
 UNIT = "pair-frames/s"
 
@@ -55,8 +65,25 @@ def parse_args():
     ap.add_argument("--no-stage3", action="store_true", help="skip the stage-3 (Pearson / covariance / frame-frame) leg")
     ap.add_argument("--stage3-frames", type=int, default=50000)
     ap.add_argument("--no-xtc", action="store_true", help="skip the trajectory-feed leg (xtc decode on the GPU vs host threads)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the configs[1] (ubiquitin) and configs[4] (interface) legs")
+    ap.add_argument("--config", default=None, choices=["c2", "c5"], help="run only that configuration's leg and print its line")
     ap.add_argument("--xtc-frames", type=int, default=2500)
     return ap.parse_args()
+
+
+def measured_traffic(kernel, nres, pair_frames):
+    """dram__bytes_read + dram__bytes_write of `kernel` per launch, scaled from the committed ncu capture of this
+    build (profiles/r2_traffic.json, written by tools/summarize_profiles.py from an `ncu --set full` run of the
+    benchmark shard); None when there is no capture for this system size."""
+    path = os.path.join(ROOT, "profiles", "r2_traffic.json")
+    try:
+        with open(path) as f:
+            rec = json.load(f).get(kernel)
+    except (OSError, ValueError):
+        return None
+    if not rec or rec.get("nres") != nres:
+        return None
+    return rec["dram_bytes"] / rec["pair_frames"] * pair_frames
 
 
 def peaks():
@@ -171,20 +198,22 @@ def run_reference(args):
     nf = max(threads, min(args.cpu_frames * 4, 256))
     xyz, res_start, _ = synth.make_trajectory(args.nres, nf, ATOMS_PER_RES, seed=4)
     P = args.nres * (args.nres - 1) // 2
-    for _ in range(max(1, min(args.warmup, 1))):
+    # every step is one pass over the same bounded sample (sized so that --steps 20 --warmup 3 ends in minutes)
+    for _ in range(max(0, args.warmup)):
         cpu_pass(xyz, res_start, threads)
-    times = [cpu_pass(xyz, res_start, threads) for _ in range(max(1, min(args.steps, 3)))]
+    times = [cpu_pass(xyz, res_start, threads) for _ in range(max(1, args.steps))]
     t = float(np.mean(times))
     value = P * nf / t
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": len(times), "warmup": 1, "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
+        "steps": len(times), "warmup": max(0, args.warmup), "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32+u16", "data": "synthetic",
         "config": {"workload": "C4 shard sample: %d residues x %d frames (of %d per GPU)" % (args.nres, nf, args.frames),
                    "nres": args.nres, "atoms_per_res": ATOMS_PER_RES, "trunc": TRUNC, "nlevels": NLEVELS},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": "%d frames of the %d-residue system, frames split over %d threads; gmx mdmat and "
-                                   "conan.py themselves are unavailable on this box" % (nf, args.nres, threads)},
+                                   "conan.py themselves are unavailable on this box" % (nf, args.nres, threads),
+                         "reference_conan_py": REFERENCE_CONAN_PY},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -212,8 +241,21 @@ def run_ours(args):
     lib = _lib.load()
 
     nf, nres = args.frames, args.nres
-    # one long trajectory, each rank generating its own frame range statistics (independent seeds)
-    xyz, res_start, _ = synth.make_trajectory(nres, nf, ATOMS_PER_RES, seed=4 + rank)
+    shard_check = None
+    if world > 1:
+        # correctness of the sharded path on this many GPUs, before anything is timed
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import sharded_check
+        shard_check = sharded_check.check(dev)
+        ok = torch.tensor([1 if (shard_check is None or shard_check["ok"]) else 0], device=dev)
+        dist.broadcast(ok, src=0)
+        if not int(ok.item()):
+            if rank == 0:
+                print(json.dumps({"sharded_check": shard_check, "error": "sharded results differ from one GPU"}), flush=True)
+            dist.destroy_process_group()
+            raise SystemExit(1)
+    # one long trajectory of nf * world frames (one seed); every rank takes its own consecutive frame range
+    xyz, res_start, _ = synth.make_trajectory(nres, nf * world, ATOMS_PER_RES, seed=4, frame_range=(rank * nf, (rank + 1) * nf))
     geom = stage1.Geometry(res_start)
     P = geom.P
     lo, hi, eq = thresholds()
@@ -239,7 +281,7 @@ def run_ours(args):
         launches[0] += 2
         if world > 1:
             sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
-            launches[0] += 4
+            launches[0] += 4           # shard summary + entering status + streaming pass + combine (collectives are NCCL's)
         else:
             stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2)
             launches[0] += 3
@@ -283,39 +325,73 @@ def run_ours(args):
     ms_stats = time_region(lambda: stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2), reps)
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- end to end from host memory --------------------------------------------------------
-    batch = max(1, min(args.batch, nf))
-    # the first copy cannot hide behind compute, so the batches start small and double up to the full size
-    edges, size = [0], min(batch, 128)
-    while edges[-1] < nf:
-        edges.append(min(nf, edges[-1] + size))
-        size = min(batch, size * 2)
+    # ---- end to end from host memory: the shard's .xtc bytes in, the statistics out -----------------------
+    from concurrent.futures import ThreadPoolExecutor
+    from conan_b200.xtc import XtcFile, encode_xtc
+    # The decoder works a warp per frame and is bound by the length of a frame's chain, not by the GPU: a launch
+    # takes about a millisecond however few frames it has, and it cannot run beside the distance kernel (whose
+    # CTAs hold the whole register file).  So the shard goes in few, large batches: a first one of --batch frames
+    # that gets the pipeline going, the rest in two halves.
+    first = max(1, min(args.batch, nf))
+    edges = [0, first]
+    if first < nf:
+        edges += [first + (nf - first + 1) // 2, nf] if nf - first > 1 else [nf]
+    edges = sorted(set(edges))
     nb = len(edges) - 1
+    batch = max(edges[b + 1] - edges[b] for b in range(nb))
+    def encode(b):      # one .xtc stream per batch (what a trajectory file split at those frames would hold)
+        b0, b1 = edges[b], edges[b + 1]
+        return encode_xtc(xyz[b0:b1], times=(np.arange(b0, b1, dtype=np.float32) + rank * nf) * 100.0)
+    with ThreadPoolExecutor(max_workers=min(nb, os.cpu_count() or 1)) as pool:
+        streams = list(pool.map(encode, range(nb)))
+    h_bytes = [torch.from_numpy(b).pin_memory() for b in streams]
+    h_offs = [torch.from_numpy(XtcFile(b.tobytes()).offsets.copy()).pin_memory() for b in streams]
+    del streams
+    max_bytes = max(t.numel() for t in h_bytes)
     NBUF = 4                     # staging buffers: the copies may run three batches ahead of the kernels
-    stage_buf = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(NBUF)]
+    stage_buf = [torch.empty(max_bytes, dtype=torch.uint8, device=dev) for _ in range(NBUF)]
+    stage_off = [torch.empty(batch, dtype=torch.int64, device=dev) for _ in range(NBUF)]
+    d_coords = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(2)]
+    d_status = torch.zeros(nf, dtype=torch.int32, device=dev)
     work_b = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
-    copy_stream = torch.cuda.Stream(dev)
+    copy_stream, dec_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     host_out = {n: torch.empty(getattr(out, n).shape, dtype=getattr(out, n).dtype).pin_memory()
                 for n, _ in stage2.PairStats.PAIR_FIELDS + stage2.PairStats.FRAME_FIELDS}
     d2h_bytes = sum(t.numel() * t.element_size() for t in host_out.values())
-    h2d_bytes = h_xyz.numel() * 4
+    h2d_bytes = sum(t.numel() for t in h_bytes) + sum(t.numel() * 8 for t in h_offs)
+    float_bytes = h_xyz.numel() * 4
 
-    last_use = [None] * NBUF     # the event after the last kernel that read each staging buffer (also across steps)
+    # three streams: copies run up to three batches ahead, the decoder (one warp per frame, far from filling
+    # the GPU) runs beside the distance kernel of the batch before it
+    bytes_free = [None] * NBUF   # event after the decode that read each staging buffer (also across steps)
+    coords_free = [None, None]   # event after the stage-1 launch that read each coordinate buffer
 
     def step_e2e():
-        copied = [torch.cuda.Event() for _ in range(nb)]
-        consumed = [torch.cuda.Event() for _ in range(nb)]
         for b in range(nb):
             b0, b1 = edges[b], edges[b + 1]
+            k, c = b % NBUF, b % 2
             with torch.cuda.stream(copy_stream):
-                if last_use[b % NBUF] is not None:
-                    copy_stream.wait_event(last_use[b % NBUF])
-                stage_buf[b % NBUF][: b1 - b0].copy_(h_xyz[b0:b1], non_blocking=True)
-                copied[b].record(copy_stream)
-            stream.wait_event(copied[b])
-            stage1.mdmat_frames(stage_buf[b % NBUF][: b1 - b0], None, geom, TRUNC, NLEVELS, False, levels[b0:b1], work_b, None)
-            consumed[b].record(stream)
-            last_use[b % NBUF] = consumed[b]
+                if bytes_free[k] is not None:
+                    copy_stream.wait_event(bytes_free[k])
+                stage_buf[k][: h_bytes[b].numel()].copy_(h_bytes[b], non_blocking=True)
+                stage_off[k][: b1 - b0].copy_(h_offs[b], non_blocking=True)
+                copied = torch.cuda.Event()
+                copied.record(copy_stream)
+            with torch.cuda.stream(dec_stream):
+                dec_stream.wait_event(copied)
+                if coords_free[c] is not None:
+                    dec_stream.wait_event(coords_free[c])
+                _lib.check(lib.conan_xtc_decode_device(stage_buf[k].data_ptr(), h_bytes[b].numel(), stage_off[k].data_ptr(), b1 - b0,
+                                                       geom.natoms, None, geom.natoms, d_coords[c].data_ptr(),
+                                                       d_status[b0:b1].data_ptr(), dec_stream.cuda_stream))
+                decoded = torch.cuda.Event()
+                decoded.record(dec_stream)
+            bytes_free[k] = decoded
+            stream.wait_event(decoded)
+            stage1.mdmat_frames(d_coords[c][: b1 - b0], None, geom, TRUNC, NLEVELS, False, levels[b0:b1], work_b, None)
+            done = torch.cuda.Event()
+            done.record(stream)
+            coords_free[c] = done
         if world > 1:
             sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
         else:
@@ -326,6 +402,7 @@ def run_ours(args):
     for _ in range(2):
         step_e2e()
     barrier()
+    assert int(d_status.abs().sum().item()) == 0, "the GPU decoder rejected a frame of its own encoder's stream"
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record(stream)
     for _ in range(args.steps):
@@ -336,9 +413,12 @@ def run_ours(args):
 
     # ---- reduce over ranks -----------------------------------------------------------------
     t = torch.tensor([ms, ms_e2e, ms_tile, ms_stats, ms_prep], dtype=torch.float64, device=dev)
+    per_rank = [t.clone() for _ in range(world)]
     if world > 1:
+        dist.all_gather(per_rank, t)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e, ms_tile, ms_stats, ms_prep = [float(v) for v in t.cpu()]
+    per_rank = [[float(v) for v in r.cpu()] for r in per_rank]
 
     if rank == 0:
         pk, pk_kind = peaks()
@@ -362,20 +442,24 @@ def run_ours(args):
                 "trunc": TRUNC, "nlevels": NLEVELS, "trunc_inter": TRUNC_INTER, "trunc_inter_high": TRUNC_INTER_HIGH,
                 "sharding": "frames x%d" % world,
                 "l2": "inputs larger than L2 (%.1f GB coordinates, %.1f GB levels per GPU); no flush needed"
-                      % (h2d_bytes / 1e9, levels.numel() * 2 / 1e9),
+                      % (float_bytes / 1e9, levels.numel() * 2 / 1e9),
             },
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                    "ms_per_step": ms_e2e / args.steps},
+                    "ms_per_step": ms_e2e / args.steps,
+                    "input": "compressed .xtc bytes of the shard (%.2f B per atom instead of 12 as float32), pinned host memory, "
+                             "decoded on the GPU; per rank" % (h2d_bytes / float(nf * geom.natoms)),
+                    "h2d_gbs_per_rank": h2d_bytes / (ms_e2e / args.steps * 1e-3) / 1e9},
+            "per_rank_ms": {"step": [r[0] / args.steps for r in per_rank], "e2e_step": [r[1] / args.steps for r in per_rank],
+                            "mdmat_tile_kernel": [r[2] for r in per_rank], "pair_stats": [r[3] for r in per_rank]},
             "gpu_launches": n_launch,
             "clocks": clocks,
             "roofline": {
                 "kernel": "mdmat_tile_kernel", "bound": "fp32", "achieved": tile_tflops, "peak": fp32_peak.value,
                 "unit": "TFLOP/s", "frac": tile_tflops / fp32_peak.value if fp32_peak.value else None,
-                # dram__bytes_read + dram__bytes_write of this kernel per pair-frame, from the committed ncu
-                # capture (profiles/r1_ncu_full_summary.txt: 0.336 GB + 0.944 GB per 1000 frames x 499 500 pairs)
-                "traffic": 2.564 * P * nf if (nres, ATOMS_PER_RES) == (1000, 8) else None, "traffic_unit": "bytes per launch",
+                "traffic": measured_traffic("mdmat_tile_kernel", nres, float(P) * nf), "traffic_unit": "bytes per launch",
                 "ms": ms_tile,
-                "peak_source": "FP32 FMA rate measured in this run (conan_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
+                "peak_source": "FP32 FMA rate measured in this run (conan_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 "
+                               "entry, profiles/r2_fp32_peak.json keeps the value of the round's runs",
                 "algorithmic": "8 flop x %.4g atom pairs (%.1f%% of residue pairs survive pruning)"
                                % (cnt[2], 100.0 * cnt[1] / (float(P) * nf)),
                 "hbm_view": {"achieved": 2.0 * P * nf / (ms_tile * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
@@ -383,12 +467,13 @@ def run_ours(args):
             },
             "roofline_stats": {"kernel": "pair_stats_kernel (+combine)", "bound": "hbm", "achieved": stats_gbs,
                                "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": stats_gbs / pk["hbm_gbs"],
-                               # 1.0155 GB read + 0.126 GB written per 1000 frames x 499 500 pairs (same capture)
-                               "traffic": 2.286 * P * nf if nres == 1000 else None, "traffic_unit": "bytes per launch",
+                               "traffic": measured_traffic("pair_stats_kernel", nres, float(P) * nf), "traffic_unit": "bytes per launch",
                                "ms": ms_stats, "peak_kind": pk_kind},
             "stage_ms": {"prep_slots_kernel": ms_prep, "mdmat_tile_kernel": ms_tile, "pair_stats": ms_stats},
             "boundary_results": int(cnt[0]),
         }
+        if shard_check is not None:
+            line["sharded_check"] = shard_check
         if not args.no_cpu_baseline:
             ncpu = max(4, args.cpu_frames)
             t_cpu = cpu_pass(xyz[:ncpu], res_start, 1)
@@ -398,10 +483,13 @@ def run_ours(args):
                           "gmx mdmat itself: unavailable on this box" % (ncpu, nres, t_cpu, os.cpu_count() or 0)}
         if not args.no_xtc:
             line["xtc_feed"] = run_xtc_feed(args, dev, xyz)
+        del d_xyz, levels, work1, work2, stage_buf, d_coords, work_b
+        torch.cuda.empty_cache()
         if not args.no_stage3:
-            del d_xyz, levels, work1, work2
-            torch.cuda.empty_cache()
             line["stage3"] = run_stage3(args, dev)
+        if not args.no_configs:
+            line["c2"] = run_c2(dev)
+            line["c5"] = run_c5(dev)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -556,10 +644,157 @@ def run_stage3(args, dev):
     }
 
 
+def run_c2(dev):
+    """BASELINE.json configs[1]: the reference's ubiquitin unfolding trajectory (tests/golden/ubi_pull_500ps.xtc,
+    472 frames x 1231 atoms, 76 residues / 602 heavy atoms) with fine.inp's settings: trajectory bytes -> periodic
+    stage 1 -> stage 2 -> frame-frame distances for K_TRAJ_CLUSTERS, whole run, next to the CPU port of the same
+    stages on one core and to the command-line run (`conan.py`, text outputs included)."""
+    import shutil
+    import tempfile
+    import torch
+    from conan_b200 import stage1, stage2, stage3, topology
+    from conan_b200.levels import legend_values, level_thresholds
+    from conan_b200.xtc import XtcFile
+    golden = os.path.join(ROOT, "tests", "golden")
+    traj, pdb = os.path.join(golden, "ubi_pull_500ps.xtc"), os.path.join(golden, "ubi.pdb")
+    if not (os.path.exists(traj) and os.path.exists(pdb)):
+        return {"unavailable": "tests/golden/ubi_pull_500ps.xtc missing"}
+    values = legend_values(TRUNC, NLEVELS)
+    lo, hi, eq = level_thresholds(values, 0.5, 0.5)        # TRUNC_INTER 0.5, no upper cut-off: no hysteresis buffer
+    stream = torch.cuda.current_stream(dev)
+
+    def whole_run():
+        top = topology.read_topology(pdb)
+        x = XtcFile(traj)
+        sel = top.default_groups()[2][1]
+        geom = stage1.Geometry(top.residue_runs(sel))
+        d_xyz = x.decode_device(atom_sel=sel, device=dev)
+        d_box = torch.from_numpy(np.ascontiguousarray(x.boxes).reshape(-1, 9)).to(dev)
+        levels = torch.zeros((x.nframes, geom.stride), dtype=torch.uint16, device=dev)
+        work = torch.empty(stage1.mdmat_workspace_bytes(x.nframes, geom), dtype=torch.uint8, device=dev)
+        stage1.mdmat_frames(d_xyz, d_box, geom, TRUNC, NLEVELS, True, levels, work, None)
+        st = stage2.pair_stats(levels, geom.P, NLEVELS, lo, hi, eq)
+        h = st.host()
+        seen = np.flatnonzero(h["sum_k"] < x.nframes * (NLEVELS - 1)).astype(np.int32)
+        centre = values.astype(np.float16).astype(np.float32)[np.clip(np.rint(h["sum_k"][seen] / x.nframes).astype(int), 0, NLEVELS - 1)]
+        D = stage3.frame_distances(levels, seen, NLEVELS, stage3.lut16(values, dev), centre, geom.nres / np.sqrt(2.0))
+        D.cpu()
+        return x.nframes, geom.P, x, sel, geom
+
+    whole_run()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    reps = 3
+    for _ in range(reps):
+        nf, P, x, sel, geom = whole_run()
+    torch.cuda.synchronize(dev)
+    t_gpu = (time.perf_counter() - t0) / reps
+    # the CPU port of stages 1 and 2 on the same frames, one core
+    from oracle import oracle
+    xyz = x.decode()
+    t0 = time.perf_counter()
+    full = oracle.mdmat_levels(xyz, x.boxes, sel, geom.res_start, TRUNC, NLEVELS, 1)
+    oracle.pair_stats(oracle.condensed(full), lo, hi, eq)
+    t_cpu = time.perf_counter() - t0
+    # the command line, fine.inp's keywords (MATRICES no: 472 x 2 text files of 5776 rows are formatting, not analysis)
+    work = tempfile.mkdtemp(prefix="conan_c2_")
+    with open(os.path.join(work, "fine.inp"), "w") as f:
+        f.write("TRAJ %s\nCOORD %s\nNLEVEL 1001\nDT 500\nTRUNC 1.0\nTRUNC_INTER 0.5\nTRUNC_DR 1.0\nDR_MODE init\n"
+                "K_TRAJ_CLUSTERS 1-5\nMATRICES no\nMAKE_MOVIE no\n" % (traj, pdb))
+    t0 = time.perf_counter()
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "conan.py"), "fine.inp"], cwd=work, input="2\n", capture_output=True, text=True)
+    t_cli = time.perf_counter() - t0
+    shutil.rmtree(work, ignore_errors=True)
+    return {"workload": "C2: applications/1_ubi_unfold, %d frames x %d pairs (76 residues, 602 heavy atoms), periodic box" % (nf, P),
+            "whole_run_s": t_gpu, "pair_frames_per_s": float(P) * nf / t_gpu,
+            "stages": "xtc index + GPU decode + stage 1 (minimum image) + stage 2 + frame-frame distances, results on the host",
+            "cpu_port_s": t_cpu, "cpu_port": "oracle stage 1 + stage 2, one core (gmx mdmat and conan.py: unavailable on this box; "
+                                             "conan.py's stage 2 alone is %.0f s at 32 us per pair-frame)" % (32e-6 * P * nf),
+            "cli_wall_s": t_cli, "cli_rc": r.returncode,
+            "cli": "conan.py with fine.inp's keywords, K_TRAJ_CLUSTERS 1-5, MATRICES no; process start, import torch and "
+                   "all text outputs included"}
+
+
+def run_c5(dev):
+    """BASELINE.json configs[4]: two chains of 200 and 400 residues, 20 000 frames, X x Y block only (80 000 pairs),
+    stage 1 + stage 2 and the frame-frame distance matrix of K_TRAJ_CLUSTERS over the pairs that ever touch."""
+    import torch
+    from conan_b200 import stage1, stage2, stage3, synth
+    from conan_b200.levels import legend_values, level_thresholds
+    nx, ny, nf = 200, 400, 20000
+    xyz, res_start, _ = synth.make_trajectory(nx + ny, nf, ATOMS_PER_RES, seed=5, two_chain=(nx, ny))
+    geom = stage1.Geometry(res_start, 0, nx, nx, ny)
+    P = geom.P
+    values = legend_values(TRUNC, NLEVELS)
+    lo, hi, eq = level_thresholds(values, TRUNC_INTER, TRUNC_INTER_HIGH)
+    d_xyz = torch.from_numpy(xyz).to(dev)
+    del xyz
+    levels = torch.zeros((nf, geom.stride), dtype=torch.uint16, device=dev)
+    work1 = torch.empty(stage1.mdmat_workspace_bytes(nf, geom), dtype=torch.uint8, device=dev)
+    work2 = torch.empty(stage2.pair_stats_workspace_bytes(nf, P), dtype=torch.uint8, device=dev)
+    out = stage2.PairStats(nf, P, dev)
+    counters = torch.zeros(3, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize(dev)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            fn()
+        b.record(stream)
+        torch.cuda.synchronize(dev)
+        return a.elapsed_time(b) / reps
+
+    stage1.mdmat_frames(d_xyz, None, geom, TRUNC, NLEVELS, False, levels, work1, counters)
+    ms1 = timed(lambda: stage1.mdmat_frames(d_xyz, None, geom, TRUNC, NLEVELS, False, levels, work1, None))
+    ms2 = timed(lambda: stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2))
+    del d_xyz, work1
+    h = out.host()
+    seen = np.flatnonzero(h["sum_k"] < nf * (NLEVELS - 1)).astype(np.int32)
+    centre = values.astype(np.float16).astype(np.float32)[np.clip(np.rint(h["sum_k"][seen] / nf).astype(int), 0, NLEVELS - 1)]
+    lut = stage3.lut16(values, dev)
+    norm = float(np.sqrt(nx * ny))                                       # conan.py:2038-2039
+    d_sel = torch.from_numpy(seen).to(dev)
+    d_mean = torch.from_numpy(centre).to(dev)
+    ms_op = timed(lambda: stage3.build_operand(levels, d_sel, NLEVELS, lut, d_mean, rows_are_frames=True, scale=1.0 / norm), reps=2)
+    fh, fl, n2, sf = stage3.build_operand(levels, d_sel, NLEVELS, lut, d_mean, rows_are_frames=True, scale=1.0 / norm)
+    D = torch.empty((nf, nf), dtype=torch.float32, device=dev)
+    ms_ff = timed(lambda: stage3.gemm_3xtf32(fh, fl, fh, fl, len(seen), epilogue=1, alpha=1.0 / sf, row_norm2=n2, col_norm2=n2,
+                                             symmetric=True, out=D), reps=2)
+    cnt = counters.cpu().numpy().astype(np.float64)
+    total = ms1 + ms2 + ms_op + ms_ff
+    return {"workload": "C5: %d x %d residue interface, %d frames, %d pairs (block mode), %d of them ever within trunc" % (nx, ny, nf, P, len(seen)),
+            "stage1_ms": ms1, "stage2_ms": ms2, "operand_ms": ms_op, "frame_frame_ms": ms_ff, "frame_frame_rows": nf, "frame_frame_k": int(len(seen)),
+            "survivor_frac": cnt[1] / (float(P) * nf), "pair_frames_per_s_stage12": float(P) * nf / ((ms1 + ms2) * 1e-3),
+            "pair_frames_per_s_with_frame_frame": float(P) * nf / (total * 1e-3),
+            "frame_frame_useful_tflops": 1.0 * nf * nf * len(seen) / ms_ff / 1e9}
+
+
+def run_config_only(args):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for --impl ours)")
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    rec = run_c2(dev) if args.config == "c2" else run_c5(dev)
+    if args.config == "c2":
+        value, ms = rec.get("pair_frames_per_s"), 1e3 * rec.get("whole_run_s", 0.0)
+    else:
+        value, ms = rec["pair_frames_per_s_with_frame_frame"], rec["stage1_ms"] + rec["stage2_ms"] + rec["operand_ms"] + rec["frame_frame_ms"]
+    print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": 3, "warmup": 1, "ms_per_step": ms,
+                      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+u16",
+                      "data": "reference trajectory" if args.config == "c2" else "synthetic",
+                      "config": {"workload": rec["workload"]}, args.config: rec}), flush=True)
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.config:
+        run_config_only(args)
     else:
         run_ours(args)
 

@@ -160,7 +160,7 @@ struct DecodeParams {
 // 32 groups at a time, all lanes in step on the same few bits (the chain is ~20 instructions and one
 // cached load per group instead of the whole decode), and lane g keeps the description of group g;
 // then the 32 groups are decoded in parallel, one per lane.
-__global__ void __launch_bounds__(kDecodeThreads) xtc_decode_kernel(const DecodeParams prm) {
+__global__ void __launch_bounds__(kDecodeThreads, 8) xtc_decode_kernel(const DecodeParams prm) {
     const int lane = threadIdx.x & 31;
     const int64_t f = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (f >= prm.nframes) return;

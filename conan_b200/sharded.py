@@ -8,80 +8,85 @@ frame range.  Stage 2 needs three small exchanges:
      has a frame outside the hysteresis buffer and the status it then leaves with
      (conan_shard_summary, a short backward scan from the shard's end); an exclusive scan over
      ranks gives the status entering every shard before the streaming pass runs;
-  3. the per-pair sums: all-reduce SUM of the integer moments and counts, MIN / MAX of the
-     first / last frame and level extremes.  Integer sums make the merge exact and
+  3. the per-pair sums: all-reduce SUM of the integer moments and counts, MAX of the last frame,
+     the decided flag and the negated first frame.  Integer sums make the merge exact and
      order-independent.
+Exchanges 1 and 2 travel in one all-gather of a packed record per rank, exchange 3 in two all-reduces
+over packed buffers.
 The collectives are torch.distributed (NCCL over NVLink on the GPUs, gloo in the CPU tests).
 """
 import torch
 import torch.distributed as dist
 
-_INT_MAX = 2 ** 31 - 1
+_INT_MIN = -(2 ** 31)
 
 
-def _raw(t):
-    """Byte view for pure data movement (the collectives have no 16-bit unsigned type)."""
-    return t.contiguous().view(torch.uint8)
+def exchange_summaries(first_row_local, last_row_local, decided, status_out, group=None):
+    """ONE all-gather of every rank's packed record (first row, last row, decided, status: 6 bytes per pair)
+    -> (row of global frame 0, last row of the preceding rank or None, status entering this rank, status after
+    the last rank's last frame).
 
-
-def exchange_rows(first_row_local, last_row_local, group=None):
-    """-> (row of global frame 0, last row of the preceding rank or None for rank 0)."""
+    The two status results are the exclusive / inclusive scan of the shards' (decided, status) summaries: a
+    shard that has a frame outside the hysteresis buffer leaves with its own status whatever it entered with."""
     rank, world = dist.get_rank(group), dist.get_world_size(group)
-    first = _raw(first_row_local).clone()
-    dist.broadcast(first, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-    mine = _raw(last_row_local)
-    lasts = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(lasts, mine, group=group)
-    prev = lasts[rank - 1] if rank > 0 else None
-    back = lambda t: t.view(first_row_local.dtype)
-    return back(first), (None if prev is None else back(prev))
-
-
-def entering_status(decided, status_out, group=None):
-    """Exclusive scan of the shards' (decided, status) summaries -> status entering this rank."""
-    rank, world = dist.get_rank(group), dist.get_world_size(group)
-    dec = [torch.empty_like(decided) for _ in range(world)]
-    sta = [torch.empty_like(status_out) for _ in range(world)]
-    dist.all_gather(dec, decided.contiguous(), group=group)
-    dist.all_gather(sta, status_out.contiguous(), group=group)
-    s = torch.zeros_like(status_out)
+    P = decided.numel()
+    u8 = lambda t: t.contiguous().view(torch.uint8).reshape(-1)         # the collectives have no 16-bit unsigned type
+    rec = torch.cat([u8(first_row_local[:P]), u8(last_row_local[:P]), u8(decided), u8(status_out)])
+    recs = [torch.empty_like(rec) for _ in range(world)]
+    dist.all_gather(recs, rec, group=group)
+    row = lambda r, k: recs[r][2 * P * k:2 * P * (k + 1)].view(first_row_local.dtype)
+    dec = lambda r: recs[r][4 * P:5 * P]
+    sta = lambda r: recs[r][5 * P:6 * P]
+    s_in = torch.zeros_like(status_out)
     for q in range(rank):
-        s = torch.where(dec[q] != 0, sta[q], s)
-    return s
+        s_in = torch.where(dec(q) != 0, sta(q), s_in)
+    s_end = s_in
+    for q in range(rank, world):
+        s_end = torch.where(dec(q) != 0, sta(q), s_end)
+    return row(0, 0), (row(rank - 1, 1) if rank > 0 else None), s_in, s_end
 
 
-def merge_pair_stats(st, group=None):
-    """All-reduce the per-pair fields of `st` (an object with tensor attributes) in place."""
-    world = dist.get_world_size(group)
-    for name in ("sum_k", "sum_k2", "n_int", "n_enc"):
-        dist.all_reduce(getattr(st, name), op=dist.ReduceOp.SUM, group=group)
+def merge_pair_stats(st, final_status=None, group=None):
+    """Two all-reduces over packed buffers bring the per-pair fields of `st` (an object with tensor attributes)
+    to the values of a single run: SUM over (sum_k, sum_k2, n_int, n_enc), MAX over (last_f, decided, -first_f)
+    with "never" mapped to the smallest integer.  The status after the last frame is the last shard's; it comes
+    out of the summary scan (final_status) without another collective."""
+    sums = torch.stack([st.sum_k, st.sum_k2, st.n_int.to(torch.int64), st.n_enc.to(torch.int64)])
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    st.sum_k.copy_(sums[0]); st.sum_k2.copy_(sums[1]); st.n_int.copy_(sums[2]); st.n_enc.copy_(sums[3])
     first = st.first_f
-    first.copy_(torch.where(first < 0, torch.full_like(first, _INT_MAX), first))
-    dist.all_reduce(first, op=dist.ReduceOp.MIN, group=group)
-    first.copy_(torch.where(first == _INT_MAX, torch.full_like(first, -1), first))
-    dist.all_reduce(st.last_f, op=dist.ReduceOp.MAX, group=group)
-    dist.all_reduce(st.decided, op=dist.ReduceOp.MAX, group=group)
-    # the status after the last frame is the last shard's
-    src = dist.get_global_rank(group, world - 1) if group is not None else world - 1
-    dist.broadcast(st.status, src=src, group=group)
+    neg_first = torch.where(first < 0, torch.full_like(first, _INT_MIN), -first)
+    maxs = torch.stack([st.last_f, st.decided.to(torch.int32), neg_first])
+    dist.all_reduce(maxs, op=dist.ReduceOp.MAX, group=group)
+    st.last_f.copy_(maxs[0])
+    st.decided.copy_(maxs[1])
+    first.copy_(torch.where(maxs[2] == _INT_MIN, torch.full_like(first, -1), -maxs[2]))
+    if final_status is not None:
+        st.status.copy_(final_status)
+    else:
+        world = dist.get_world_size(group)
+        src = dist.get_global_rank(group, world - 1) if group is not None else world - 1
+        dist.broadcast(st.status, src=src, group=group)
     return st
 
 
 def pair_stats_sharded(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0, out=None, work=None, group=None,
                        local_pass=None, local_summary=None):
-    """Stage 2 over this rank's frame shard, merged so that per-pair results equal a single run.
+    """Stage 2 over this rank's frame shard, merged so that per-pair results equal a single run: one all-gather
+    before the streaming pass, two all-reduces after it.
 
     Per-frame results stay local to the rank (frames are disjoint).  `local_pass` / `local_summary`
     exist for the CPU tests: callables with the signatures of stage2.pair_stats / shard_summary."""
     if local_pass is None:
         from . import stage2
         local_pass, local_summary = stage2.pair_stats, stage2.shard_summary
-    first_row, prev_row = exchange_rows(levels[0], levels[-1], group)
     decided, status = local_summary(levels, P, nlevels, lo_cnt, hi_first, equal_cut)
-    s_in = entering_status(decided, status, group)
-    st = local_pass(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=frame0, first_row=first_row,
-                    prev_row=prev_row, status_in=s_in, out=out, work=work)
-    return merge_pair_stats(st, group)
+    first_row, prev_row, s_in, s_end = exchange_summaries(levels[0], levels[-1], decided, status, group)
+    # rows travel without their padding; the streaming pass wants 16-byte aligned rows of the stack's pitch
+    pad = lambda r: None if r is None else torch.nn.functional.pad(r.view(torch.int16), (0, levels.shape[1] - P)).view(levels.dtype)
+    st = local_pass(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=frame0, first_row=pad(first_row),
+                    prev_row=pad(prev_row), status_in=s_in, out=out, work=work)
+    return merge_pair_stats(st, s_end, group)
 
 
 # ------------------------------------------------------------------------------------------------

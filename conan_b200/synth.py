@@ -42,12 +42,15 @@ def _globule(rng, nres, density=7.0, bond=0.38, min_dist=0.30):
     return pos, R
 
 
-def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtype=np.float32, closer=0.0):
+def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtype=np.float32, closer=0.0,
+                    frame_range=None):
     """Returns (xyz [nframes, natoms, 3] float32 nm, res_start [nres+1] int32, box_length nm).
 
     two_chain=(nx, ny): two globules of nx and ny residues whose separation follows an OU process
     around 1.5 nm surface distance (the asymmetric interface configuration); closer (nm) moves the second
-    globule towards the first, for small systems that should share more than a handful of contacts."""
+    globule towards the first, for small systems that should share more than a handful of contacts.
+    frame_range=(f0, f1): only frames f0..f1-1 of the nframes-long trajectory are returned (a frame shard of
+    one long run: the random stream is advanced through the frames before it, nothing else is kept)."""
     rng = np.random.default_rng(seed)
     if two_chain is None:
         centres, R = _globule(rng, nres)
@@ -61,18 +64,26 @@ def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtyp
         R = R1 + R2 + 1.0
         shift = (nx, ny)
     offsets = rng.normal(0.0, 0.15, size=(nres, atoms_per_res, 3))
+    f_lo, f_hi = (0, nframes) if frame_range is None else (int(frame_range[0]), int(frame_range[1]))
+    assert 0 <= f_lo < f_hi <= nframes
+    nkeep = f_hi - f_lo
     a = np.exp(-1.0 / 200.0)
-    disp = np.empty((nframes, nres, 3), dtype=np.float32)
+    disp = np.empty((nkeep, nres, 3), dtype=np.float32)
     state = rng.normal(0.0, 0.1, size=(nres, 3))
     s = 0.1 * np.sqrt(1.0 - a * a)
     block = 2048
     for f0 in range(0, nframes, block):
+        if f0 >= f_hi and shift is None:
+            break                      # nothing after the shard draws from the stream in the one-chain system
         n = min(block, nframes - f0)
         noise = rng.normal(0.0, s, size=(n, nres, 3))
+        if f0 >= f_hi:
+            continue
         for k in range(n):
             state = a * state + noise[k]
-            disp[f0 + k] = state
-    t = np.arange(nframes, dtype=np.float64)
+            if f_lo <= f0 + k < f_hi:
+                disp[f0 + k - f_lo] = state
+    t = np.arange(f_lo, f_hi, dtype=np.float64)
     breathing = 1.0 + 0.04 * np.sin(2.0 * np.pi * t / max(nframes / 3.0, 50.0)) + 0.02 * t / max(nframes, 1)
     cen = centres[None, :, :] * breathing[:, None, None] + disp
     if shift is not None:
@@ -83,7 +94,8 @@ def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtyp
         for f in range(nframes):
             v = b * v + rng.normal(0.0, 0.35 * np.sqrt(1 - b * b))
             sep[f] = v
-        cen[:, nx:, 0] += sep[:, None]
+        cen[:, nx:, 0] += sep[f_lo:f_hi, None]
+    nframes = nkeep
     L = float(4.0 * R + 4.0)
     # assembled in blocks of frames: the float64 intermediate of a 12 500-frame shard would be 2.4 GB
     xyz = np.empty((nframes, nres * atoms_per_res, 3), dtype=dtype)

@@ -114,8 +114,8 @@ class XtcFile:
         return out
 
 
-def write_xtc(path, xyz, boxes=None, times=None, steps=None, precision=1000.0):
-    """Write float32 [nf, natoms, 3] coordinates (nm) as an .xtc trajectory."""
+def encode_xtc(xyz, boxes=None, times=None, steps=None, precision=1000.0):
+    """float32 [nf, natoms, 3] coordinates (nm) -> the bytes of an .xtc trajectory (uint8 array)."""
     lib = _lib.load()
     xyz = np.ascontiguousarray(xyz, dtype=np.float32)
     nf, na = xyz.shape[0], xyz.shape[1]
@@ -129,6 +129,12 @@ def write_xtc(path, xyz, boxes=None, times=None, steps=None, precision=1000.0):
     _lib.check(lib.conan_xtc_encode(*args, None, 0, ctypes.byref(need)))
     buf = np.empty(need.value, np.uint8)
     _lib.check(lib.conan_xtc_encode(*args, buf.ctypes.data, buf.size, ctypes.byref(need)))
+    return buf
+
+
+def write_xtc(path, xyz, boxes=None, times=None, steps=None, precision=1000.0):
+    """Write float32 [nf, natoms, 3] coordinates (nm) as an .xtc trajectory; returns the file size."""
+    buf = encode_xtc(xyz, boxes, times, steps, precision)
     with open(path, "wb") as f:
         f.write(buf.tobytes())
-    return need.value
+    return int(buf.size)
