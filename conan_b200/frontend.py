@@ -610,8 +610,6 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
     global _last_stage2
     import torch
     from . import stage1, stage2
-    if dimer:
-        print("Dimer mode is not available in this implementation; continuing without it.")
     dev = torch.device(device)
     asymm = bool(asymm_data)
     s1 = _last_stage1
@@ -682,8 +680,29 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
 
     values = lv.legend_values(trunc, nlevels)
     lo, hi, eq = lv.level_thresholds(values, trunc_inter, trunc_inter_high)
+    if dimer and asymm and xres == yres:
+        # DIMER (conan.py:553-565): every frame is oriented so that the weighted contacts above the diagonal of
+        # its X x Y block are the heavier half; the statistics run on the oriented frames
+        lib = _lib.load()
+        flipped = torch.zeros(nf, dtype=torch.uint8, device=dev)
+        _lib.check(lib.conan_dimer_orient(d_stack.data_ptr(), stride, nf, xres, nlevels, flipped.data_ptr(),
+                                          torch.cuda.current_stream(dev).cuda_stream))
+        print("Dimer mode: %d of %d frames were transposed." % (int(flipped.sum().item()), nf))
+    elif dimer:
+        print("'Dimer mode' requires the asymmetric mode with identical X- and Y- residue ranges; it is ignored here.")
+        dimer = False
     st = stage2.pair_stats(d_stack, P, nlevels, lo, hi, eq)
     stats = st.host()
+    if dimer:
+        # rmsd_frame's dimer branch (:1420-1428): the smaller of the distance to a frame and to its transpose
+        tp = torch.zeros(nf, dtype=torch.int64, device=dev)
+        t0 = torch.zeros(nf, dtype=torch.int64, device=dev)
+        _lib.check(lib.conan_dimer_ssd(d_stack.data_ptr(), stride, nf, xres, 0, 0, tp.data_ptr(), t0.data_ptr(),
+                                       torch.cuda.current_stream(dev).cuda_stream))
+        tp, t0 = tp.cpu().numpy(), t0.cpu().numpy()
+        tp[0] = stats["ssd_prev"][0]                       # no frame before the first one
+        stats["ssd_prev"] = np.minimum(stats["ssd_prev"], tp)
+        stats["ssd_first"] = np.minimum(stats["ssd_first"], t0)
     tab = tables.Stage2Tables(stats, values, time_vec, trunc, layout)
     for d in ("aggregate", "matrices"):
         os.makedirs(d, exist_ok=True)
@@ -809,6 +828,8 @@ def main(argv=None):
         sys.exit()
     with open(argv[1]) as finput:
         opts = read_options(finput, opts)
+    from .compat import publish_globals
+    publish_globals(opts)          # every keyword becomes a module attribute, as conan.py:1748 does
     g = opts
     asymm_data = None
     if g['asymm']:
@@ -868,6 +889,10 @@ def main(argv=None):
                               g['trunc_lifetime'], matrices=g['matrices'], nterm=nterm)
     if inputf is not None:
         inputf.close()
+    # the script-level names the reference's helper functions read
+    publish_globals({'nres': nres, 'nlevels': nlevels, 'nchar': nchar, 'dict_legend': dict_legend, 'trunc': trunc, 'nterm': nterm,
+                     'trunc_dr': trunc_dr, 'trunc_inter': trunc_inter, 'trunc_inter_high': trunc_inter_high,
+                     'time_vec': ret[2], 'pairs_list': ret[3], 'pairs_legend': ret[4], 'vectors': ret[5], 'nframes': len(ret[2])})
     from . import analyses
     g['_trunc_inter_high'] = trunc_inter_high
     analyses.run_all(g, ret, _last_stage2, trunc, trunc_inter, nres, nterm, asymm_data)

@@ -226,6 +226,23 @@ int conan_shard_summary(const uint16_t* d_levels, int64_t levels_stride, int64_t
                         int32_t nlevels, int32_t lo_cnt, int32_t hi_first, int32_t equal_cut,
                         uint8_t* d_decided, uint8_t* d_status, void* stream);
 
+/*
+ * DIMER mode (conan.py:553-565 in read_frame, :1420-1428 in rmsd_frame): the stack holds n x n blocks of a
+ * homodimer run (X and Y residues carry the same labels).
+ * conan_dimer_orient transposes, in place, every frame whose weighted contacts below the diagonal outweigh
+ * those above it (weights in exact level units, maxlevel - k); d_flipped [nf] (optional) tells which.  Run it
+ * before conan_pair_stats: the reference's statistics are taken on the oriented frames.
+ * conan_dimer_ssd gives the transposed twins of conan_pair_stats' per-frame sums: sum over the block of
+ * (k_f[x][y] - k_ref[y][x])^2 against the previous frame (d_prev_row for the first frame of the call, NULL =
+ * none, result 0) and against global frame 0 (d_first_row, NULL = row 0); the reference reports the smaller
+ * of the plain and the transposed distance.
+ */
+int conan_dimer_orient(uint16_t* d_levels, int64_t levels_stride, int64_t nf, int32_t n, int32_t nlevels,
+                       uint8_t* d_flipped, void* stream);
+int conan_dimer_ssd(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int32_t n,
+                    const uint16_t* d_first_row, const uint16_t* d_prev_row, int64_t* d_ssd_prev_t,
+                    int64_t* d_ssd_first_t, void* stream);
+
 /* ------------------------------------------------------------------------------------ */
 /* Stage 3: the dense analyses over the level stack.  The float16 `vectors` array of the   */
 /* reference (conan.py:731, :821-826) is never materialised: values come from a table of  */

@@ -18,6 +18,7 @@ Fixtures written
   case_ubi.npz          outputs of the unmodified reference on that trajectory with the keywords of
                         applications/1_ubi_unfold/fine.inp plus a STAGES file; its dmf.xpm comes from the CPU
                         restatement of gmx mdmat (oracle/), since gmx itself is unavailable
+  case_dimer.npz        DIMER yes on a small homodimer-like stack with a third of the frames transposed
   case_c5.npz           the same for a small two-chain interface system (50 x 100 residues, 200 frames) in the
                         asymmetric mode with K_TRAJ_CLUSTERS 2-5: BASELINE.json configs[4] scaled to what the
                         reference finishes in a minute
@@ -199,10 +200,32 @@ def c5_case():
     np.savez_compressed(os.path.join(OUT, "case_c5.npz"), **c)
 
 
+def dimer_case():
+    """DIMER yes on a 2 x 6 residue system whose X x Y block is handed to the reference transposed in a third
+    of the frames (the two chains exchanged): read_frame's orientation (conan.py:553-565) and the dimer branch of
+    rmsd_frame (:1420-1428)."""
+    nf, n, nl = 40, 6, 101
+    full = synthetic_levels(21, nf, 2 * n, nl, 0.5, 0.6)
+    rng = np.random.default_rng(22)
+    swap = rng.random(nf) < 0.35
+    for f in np.flatnonzero(swap):
+        blk = full[f, :n, n:].copy()
+        full[f, :n, n:] = blk.T
+        full[f, n:, :n] = blk
+    run_case("dimer", full, np.arange(nf) * 100, 1.0, nl,
+             "TRUNC_INTER 0.5\nTRUNC_INTER_HIGH 0.6\nSTART_X 1\nNRES_X %d\nNTERM_X 1\nSTART_Y %d\nNRES_Y %d\nNTERM_Y 1\n"
+             "DIMER yes\nDR_MODE both\n" % (n, n + 1, n))
+    c = dict(np.load(os.path.join(OUT, "case_dimer.npz")))
+    c["in/swapped_frames"] = swap
+    np.savez_compressed(os.path.join(OUT, "case_dimer.npz"), **c)
+
+
 def main():
     if not ref_runner.available():
         sys.exit("needs /root/reference")
     only = sys.argv[1] if len(sys.argv) > 1 else None
+    if only == "dimer":
+        return dimer_case()
     if only == "ubi":
         return ubi_case()
     if only == "c5":
@@ -246,6 +269,7 @@ def main():
         return
     ubi_case()
     c5_case()
+    dimer_case()
     # finer legend: 1001 levels, trunc 1.5 (dx = 0.0015, not a multiple of 1e-4)
     full2 = synthetic_levels(12, 30, 9, 1001, 0.5, 0.6)
     run_case("fine", full2, np.arange(30) * 500 + 1000, 1.5, 1001,

@@ -66,7 +66,7 @@ def test_asymmetric_from_xpm_matches_reference_goldens(lib, goldens, tmp_path):
     assert np.array_equal(np.rint(m[:, 2] * 1000).astype(int).reshape(14, 14), goldens["levels_asym"][3])
 
 
-@pytest.mark.parametrize("case", ["hyst", "equalcut", "default", "asym", "fine"])
+@pytest.mark.parametrize("case", ["hyst", "equalcut", "default", "asym", "fine", "dimer"])
 def test_cases_generated_by_the_live_reference(lib, tmp_path, case):
     """Synthetic stacks with hysteresis etc.; expected files were produced by the unmodified reference."""
     from conan_b200 import xpm
