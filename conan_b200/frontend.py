@@ -251,15 +251,39 @@ def handle_backups():
 class Stage1Result:
     """What `gmx mdmat` would have left in dmf.xpm, kept on the GPU: full nres x nres geometry."""
 
-    def __init__(self, levels, geom, times, trunc, nlevels, n_boundary):
+    def __init__(self, levels, geom, times, trunc, nlevels, n_boundary, shard=None):
         self.levels, self.geom, self.times = levels, geom, np.asarray(times, dtype=np.float64)
         self.trunc, self.nlevels, self.n_boundary = trunc, nlevels, n_boundary
+        # (first frame, end frame) of this rank's rows of `levels` within `times` when the run is spread over
+        # several GPUs (torch.distributed); None = all frames are here
+        self.shard = shard
 
     def square_host(self):
         """[nf, nres, nres] uint16 on the host (for dmf.xpm / matrices at small sizes)."""
         import torch
         flat = self.levels.view(torch.int16).cpu().numpy().view(np.uint16)[:, :self.geom.P]
         return xpm.square_from_condensed(flat, self.geom.nres)
+
+
+def distributed():
+    """(rank, world) when the program was started by torch.distributed.run on several GPUs (one process per
+    GPU, frames sharded over them), else (0, 1).  The process group is created on first use: NCCL, or gloo when
+    CONAN_DIST_BACKEND=gloo (several ranks on one GPU, for tests)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1:
+        return 0, 1
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        backend = os.environ.get("CONAN_DIST_BACKEND", "nccl")
+        local = int(os.environ.get("LOCAL_RANK", "0")) % max(1, torch.cuda.device_count())
+        torch.cuda.set_device(local)
+        if backend == "nccl":
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
+    return dist.get_rank(), dist.get_world_size()
 
 
 _last_stage1 = None   # handed from mdmat_run to read_process_frames within one process
@@ -345,24 +369,84 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
         print("The X / Y residue ranges do not fit the %d residues of the index group; computing all pairs." % nres_all)
         block = None
     geom = stage1.Geometry(res_start, *block) if block is not None else stage1.Geometry(res_start)
-    dev = torch.device(device)
-    levels = torch.zeros((len(frames), geom.stride), dtype=torch.uint16, device=dev)
+    rank, world = distributed()
+    dev = torch.device(device) if world == 1 else torch.device("cuda", torch.cuda.current_device())
+    shard = None
+    all_frames = frames
+    if world > 1:      # contiguous frame ranges, one per GPU; nothing is exchanged in stage 1
+        bounds = np.linspace(0, len(frames), world + 1).astype(int)
+        shard = (int(bounds[rank]), int(bounds[rank + 1]))
+        frames = frames[shard[0]:shard[1]]
+        boxes = boxes[shard[0]:shard[1]]
+        print("Rank %d of %d: frames %d .. %d of %d" % (rank, world, shard[0], shard[1] - 1, len(all_frames)))
+    levels = torch.zeros((max(len(frames), 1), geom.stride), dtype=torch.uint16, device=dev)[:len(frames)]
     counters = torch.zeros(3, dtype=torch.int64, device=dev)
     batch = max(1, min(len(frames), 2048))
     work = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
-    d_coords = torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev)
+    # The compressed frames go to the GPU as they are on disk and are decoded there (conan_xtc_decode_device).
+    # Two pinned staging buffers and a copy stream: the bytes of batch b+1 travel while batch b is decoded and
+    # its distances are computed; nothing waits on the host between batches.
+    lib = _lib.load()
+    spans = []
     for b0 in range(0, len(frames), batch):
         ids = frames[b0:b0 + batch]
-        # the compressed frames go to the GPU as they are and are decoded there (conan_xtc_decode_device)
-        d_xyz = x.decode_device(frame_ids=ids, atom_sel=sel, device=dev, out=d_coords[:len(ids)])
-        d_box = torch.from_numpy(np.ascontiguousarray(boxes[b0:b0 + batch]).reshape(-1, 9)).to(dev) if use_pbc else None
-        stage1.mdmat_frames(d_xyz, d_box, geom, trunc, nlevels, use_pbc, levels[b0:b0 + len(ids)], work, counters)
-        torch.cuda.synchronize(dev)      # the coordinate buffer is reused by the next batch
+        lo, last = int(ids.min()), int(ids.max())
+        spans.append((b0, ids, int(x.offsets[lo]), int(x.offsets[last + 1]) if last + 1 < x.nframes else int(x._buf.size)))
+    max_bytes = max((s[3] - s[2] for s in spans), default=0)
+    h_stage = [torch.empty(max_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    h_off = [torch.empty(batch, dtype=torch.int64).pin_memory() for _ in range(2)]
+    d_stage = [torch.empty(max_bytes, dtype=torch.uint8, device=dev) for _ in range(2)]
+    d_off = [torch.empty(batch, dtype=torch.int64, device=dev) for _ in range(2)]
+    d_coords = torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev)
+    d_status = torch.full((max(len(frames), 1),), -1, dtype=torch.int32, device=dev)
+    slot = np.full(x.natoms, -1, np.int32)
+    slot[np.asarray(sel, dtype=np.int64)] = np.arange(len(sel), dtype=np.int32)
+    d_slot = torch.from_numpy(slot).to(dev)
+    d_boxes = torch.from_numpy(np.ascontiguousarray(boxes, dtype=np.float32).reshape(-1, 9)).to(dev) if use_pbc else None
+    copy_stream = torch.cuda.Stream(dev)
+    main_stream = torch.cuda.current_stream(dev)
+    host_free = [None, None]      # event after the H2D copy that read each pinned buffer
+    dev_free = [None, None]       # event after the decode that read each device staging buffer
+    with torch.cuda.device(dev):
+        for n, (b0, ids, lo_b, hi_b) in enumerate(spans):
+            k = n % 2
+            if host_free[k] is not None:
+                host_free[k].synchronize()            # the pinned buffer is rewritten by the host below
+            nbytes = hi_b - lo_b
+            h_stage[k][:nbytes].numpy()[:] = x._buf[lo_b:hi_b]
+            h_off[k][:len(ids)].numpy()[:] = x.offsets[ids] - lo_b
+            with torch.cuda.stream(copy_stream):
+                if dev_free[k] is not None:
+                    copy_stream.wait_event(dev_free[k])
+                d_stage[k][:nbytes].copy_(h_stage[k][:nbytes], non_blocking=True)
+                d_off[k][:len(ids)].copy_(h_off[k][:len(ids)], non_blocking=True)
+                copied = torch.cuda.Event()
+                copied.record(copy_stream)
+            host_free[k] = copied
+            main_stream.wait_event(copied)
+            _lib.check(lib.conan_xtc_decode_device(d_stage[k].data_ptr(), nbytes, d_off[k].data_ptr(), len(ids), x.natoms,
+                                                   d_slot.data_ptr(), len(sel), d_coords.data_ptr(),
+                                                   d_status[b0:b0 + len(ids)].data_ptr(), main_stream.cuda_stream))
+            decoded = torch.cuda.Event()
+            decoded.record(main_stream)
+            dev_free[k] = decoded
+            stage1.mdmat_frames(d_coords[:len(ids)], None if d_boxes is None else d_boxes[b0:b0 + len(ids)], geom, trunc,
+                                nlevels, use_pbc, levels[b0:b0 + len(ids)], work, counters)
+    torch.cuda.synchronize(dev)
+    bad = torch.nonzero(d_status[:len(frames)]).flatten()
+    if bad.numel():
+        k = int(bad[0].item())
+        raise ConanError(-3, "frame %d of the trajectory is malformed (decoder status %d)" % (int(frames[k]), int(d_status[k].item())))
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(counters)
     nb = int(counters[0].item())
     print("Computed %d distance matrices of %d residues (%d results within 2 ulp of a level boundary)."
-          % (len(frames), geom.nres, nb))
-    _last_stage1 = Stage1Result(levels, geom, x.times[frames], trunc, nlevels, nb)
-    entries = float(len(frames)) * geom.nres * geom.nres
+          % (len(all_frames), geom.nres, nb))
+    _last_stage1 = Stage1Result(levels, geom, x.times[all_frames], trunc, nlevels, nb, shard)
+    entries = float(len(all_frames)) * geom.nres * geom.nres
+    if world > 1:
+        write_xpm = bool(write_xpm) and False      # the stack is spread over the GPUs: no dmf.xpm (WRITE_XPM is ignored)
     if write_xpm is None:
         write_xpm = entries <= XPM_WRITE_LIMIT
     if block is not None:
@@ -600,6 +684,43 @@ def _write_matrix_files(levels_host, values, layout, trunc, dr_mode, nframes, sy
                                         int(dr_mode), None, None, b"matrices", min(32, os.cpu_count() or 1)))
 
 
+def _stage2_on_shards(d_stack, P, nlevels, lo, hi, eq, frame0, nf_total, rank, world):
+    """Stage 2 when the frames are spread over several GPUs: every rank streams its own
+    shard, the per-pair sums are merged (conan_b200/sharded.py), the per-frame lines are concatenated, and the
+    level shards are collected on rank 0, which writes the tables and runs whatever analysis follows on the
+    whole stack (a 100 000-frame stack of 1000 residues is 100 GB: it fits one B200).
+    Returns (whole stack on rank 0 / own shard elsewhere, merged statistics as host arrays)."""
+    import torch
+    import torch.distributed as dist
+    from . import sharded
+    dev = d_stack.device
+    st = sharded.pair_stats_sharded(d_stack, P, nlevels, lo, hi, eq, frame0=frame0)
+    stats = st.host()
+    counts = torch.zeros(world, dtype=torch.int64, device=dev)
+    counts[rank] = d_stack.shape[0]
+    dist.all_reduce(counts)
+    counts = [int(c) for c in counts.cpu()]
+    assert sum(counts) == nf_total
+    most = max(counts)
+    for name in ("native", "nonnative", "ssd_prev", "ssd_first"):
+        t = getattr(st, name)
+        padded = torch.zeros(most, dtype=t.dtype, device=dev)
+        padded[:len(t)] = t
+        parts = [torch.empty_like(padded) for _ in range(world)]
+        dist.all_gather(parts, padded)
+        stats[name] = torch.cat([p[:n] for p, n in zip(parts, counts)]).cpu().numpy()
+    whole = torch.empty((nf_total, d_stack.shape[1]), dtype=torch.uint16, device=dev) if rank == 0 else None
+    o = 0
+    for r in range(world):         # one shard at a time travels to every rank; only rank 0 keeps it
+        part = d_stack if r == rank else torch.empty((counts[r], d_stack.shape[1]), dtype=torch.uint16, device=dev)
+        dist.broadcast(part.view(torch.uint8), src=r)
+        if rank == 0:
+            whole[o:o + counts[r]].copy_(part)
+        o += counts[r]
+        del part
+    return (whole if rank == 0 else d_stack), stats
+
+
 def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, trunc, trunc_inter, trunc_inter_high,
                         begin, end, dt, patch_time, gnus_path, dr_mode, domains, pearson_inter, economy, dimer, reread,
                         stages_list, interact_pair_dict, trunc_lifetime, matrices=True, nterm=1, device="cuda"):
@@ -669,7 +790,21 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
         sys.exit()
     time_vec = [float(t) for t in times_all[keep]]
     P, stride = layout.P, lv.padded_stride(layout.P)
-    if d_stack is not None:
+    rank, world = distributed()
+    shard = s1.shard if (s1 is not None and d_stack is not None) else None
+    frame0 = 0
+    if shard is not None:
+        # several GPUs: this rank holds rows shard[0] .. shard[1]-1 of the frame axis; the frame filter above was
+        # taken on the whole axis, so every rank agrees on which frames count and on their global numbers
+        dev = d_stack.device
+        mine = keep[(keep >= shard[0]) & (keep < shard[1])]
+        frame0 = int(np.searchsorted(keep, shard[0]))
+        if len(mine) != d_stack.shape[0]:
+            d_stack = d_stack.view(torch.int16)[torch.from_numpy(mine - shard[0]).to(dev)].contiguous().view(torch.uint16)
+        if dimer:
+            print("Dimer mode runs on one GPU only; it is switched off in this multi-GPU run.")
+            dimer = False
+    elif d_stack is not None:
         if len(keep) != d_stack.shape[0]:
             d_stack = d_stack.view(torch.int16)[torch.from_numpy(keep).to(dev)].contiguous().view(torch.uint16)
     else:
@@ -691,8 +826,13 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
     elif dimer:
         print("'Dimer mode' requires the asymmetric mode with identical X- and Y- residue ranges; it is ignored here.")
         dimer = False
-    st = stage2.pair_stats(d_stack, P, nlevels, lo, hi, eq)
-    stats = st.host()
+    if shard is not None:
+        d_stack, stats = _stage2_on_shards(d_stack, P, nlevels, lo, hi, eq, frame0, len(keep), rank, world)
+        if rank != 0:
+            return None            # rank 0 holds the merged statistics and the whole stack from here on
+        nf = d_stack.shape[0]
+    else:
+        stats = stage2.pair_stats(d_stack, P, nlevels, lo, hi, eq).host()
     if dimer:
         # rmsd_frame's dimer branch (:1420-1428): the smaller of the distance to a frame and to its transpose
         tp = torch.zeros(nf, dtype=torch.int64, device=dev)
@@ -838,7 +978,12 @@ def main(argv=None):
     interact_pair_dict = None
     trunc = g['trunc']
     trunc_input = trunc
-    handle_backups()
+    rank, world = distributed()        # several GPUs when started by torch.distributed.run: frames are sharded
+    if rank == 0:
+        handle_backups()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
     block = None
     if g['asymm'] and 'xdict' in g and 'ydict' in g and not g.get('write_xpm'):
         xs, ys = sorted(g['xdict']), sorted(g['ydict'])
@@ -868,9 +1013,10 @@ def main(argv=None):
         with open('dmf.xpm') as f:
             nres, nlevels, nchar, dict_legend, trunc = read_index(f)
         inputf = open('dmf.xpm')
-    for d in ('frames', 'matrices', 'aggregate', 'movies', 'input'):
-        os.makedirs(d, exist_ok=True)
-    shutil.copy(argv[1], 'input')
+    if rank == 0:
+        for d in ('frames', 'matrices', 'aggregate', 'movies', 'input'):
+            os.makedirs(d, exist_ok=True)
+        shutil.copy(argv[1], 'input')
     nterm = g['nterm']
     if trunc != trunc_input and g['trunc_given']:
         print("Warning! Truncation threshold given is different to the original one. Will use the given one!")
@@ -889,6 +1035,11 @@ def main(argv=None):
                               g['trunc_lifetime'], matrices=g['matrices'], nterm=nterm)
     if inputf is not None:
         inputf.close()
+    if ret is None:                # a rank other than 0 of a multi-GPU run: its part is done
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+        return None
     # the script-level names the reference's helper functions read
     publish_globals({'nres': nres, 'nlevels': nlevels, 'nchar': nchar, 'dict_legend': dict_legend, 'trunc': trunc, 'nterm': nterm,
                      'trunc_dr': trunc_dr, 'trunc_inter': trunc_inter, 'trunc_inter_high': trunc_inter_high,
@@ -896,4 +1047,8 @@ def main(argv=None):
     from . import analyses
     g['_trunc_inter_high'] = trunc_inter_high
     analyses.run_all(g, ret, _last_stage2, trunc, trunc_inter, nres, nterm, asymm_data)
+    if distributed()[1] > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
     return ret

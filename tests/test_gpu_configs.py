@@ -203,3 +203,33 @@ def test_interface_fullsize_block_mode(interface_fullsize, orc):
     want = torch.cdist(v, v)
     err = (dist.to(torch.float64) - want).norm() / want.norm()
     assert float(err) < 1e-5, float(err)
+
+
+def test_command_line_on_two_ranks_equals_one(lib, tmp_path):
+    """`conan.py` started by torch.distributed.run with two ranks (frames sharded, per-pair sums merged, rank 0
+    writes) gives the files of a single-process run.  Both ranks share this box's GPU, so the collectives go
+    through gloo here; bench.py and tools/sharded_check.py exercise the same code over NCCL on several GPUs."""
+    import socket
+    text = ("TRAJ %s/ubi_pull_500ps.xtc\nCOORD %s/ubi.pdb\nGROUP 2\nNLEVEL 1001\nTRUNC 1.0\nTRUNC_INTER 0.5\n"
+            "TRUNC_INTER_HIGH 0.6\nMATRICES no\nMAKE_MOVIE no\nPEARSON_TIME yes\nK_TRAJ_CLUSTERS 2\n" % (GOLDEN, GOLDEN))
+    one, two = tmp_path / "one", tmp_path / "two"
+    one.mkdir()
+    two.mkdir()
+    _run_cli(str(one), text)
+    with open(str(two / "test.inp"), "w") as f:
+        f.write(text)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    env = dict(os.environ, CONAN_DIST_BACKEND="gloo")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(port), os.path.join(ROOT, "conan.py"), "test.inp"], cwd=str(two), env=env,
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "Rank 1 of 2" in r.stdout
+    for name in ("aggregate/timeline.dat", "aggregate/mdmat_average_rmsf.dat", "aggregate/native_contacts.dat",
+                 "aggregate/time_mdmat_rmsd.dat", "aggregate/local_interactions.dat", "aggregate/pearson_data.dat",
+                 "cluster_trj/2/assignment.dat", "cluster_trj/rmsd_interframe.dat"):
+        a, b = np.loadtxt(str(one / name)), np.loadtxt(str(two / name))
+        assert np.array_equal(a, b), name
