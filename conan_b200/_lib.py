@@ -81,6 +81,9 @@ SIGNATURES = {
                                            c_f32, c_i32, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
     "conan_gemm_3xtf32": (ctypes.c_int, [c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_i32, c_i64, c_i64,
                                          c_i32, c_f32, c_void_p, c_void_p, c_i32, c_void_p, c_i64, c_void_p]),
+    "conan_sym_block_matvec": (ctypes.c_int, [c_void_p, c_i64, c_i32, c_void_p, c_i64, c_i32, c_void_p, c_i64, c_void_p]),
+    "conan_block_gram": (ctypes.c_int, [c_void_p, c_i64, c_i32, c_void_p, c_i64, c_i32, c_i32, c_void_p, c_void_p]),
+    "conan_block_combine": (ctypes.c_int, [c_void_p, c_i64, c_i32, c_void_p, c_i32, c_i32, c_void_p, c_i64, c_void_p]),
     "conan_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), c_void_p]),
 }
 

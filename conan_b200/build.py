@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIBPATH = os.path.join(LIBDIR, "libconan_b200.so")
-SOURCES = ["api.cu", "xtc.cpp", "xtc_gpu.cu", "textio.cpp", "mdmat.cu", "pair_stats.cu", "dimer.cu", "dense_prep.cu", "gemm3x.cu"]
+SOURCES = ["api.cu", "xtc.cpp", "xtc_gpu.cu", "textio.cpp", "mdmat.cu", "pair_stats.cu", "dimer.cu", "dense_prep.cu", "eigen.cu", "gemm3x.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--fmad=true", "-Xcompiler", "-fPIC,-O3,-pthread", "-cudart", "static",

@@ -166,46 +166,96 @@ def frame_distances(d_stack, sel, nlevels, d_lut, mean, norm):
     return gemm_3xtf32(hi, lo, hi, lo, len(sel), epilogue=1, alpha=1.0 / s, row_norm2=n2, col_norm2=n2, symmetric=True)
 
 
-def top_eigenpairs(cov, k, tol=1.0e-11, block_extra=6, depth=8, max_cycles=40, dense_below=2048):
-    """The k largest eigenpairs of a symmetric positive semi-definite device matrix: eigsh(cov, k) of
-    conan.py:1985-1990 without factorising the whole matrix.
+def _gram(u, v):
+    """u^T v for two [n, m] float64 device blocks (conan_block_gram)."""
+    lib = _lib.load()
+    g = torch.empty((u.shape[1], v.shape[1]), dtype=torch.float64, device=u.device)
+    _lib.check(lib.conan_block_gram(u.data_ptr(), u.stride(0), u.shape[1], v.data_ptr(), v.stride(0), v.shape[1], u.shape[0],
+                                    g.data_ptr(), _stream(u.device)))
+    return g
 
-    Restarted block Krylov iteration with Rayleigh-Ritz in float64: per cycle the block of Ritz vectors is
-    multiplied `depth` times by the matrix (each product re-orthonormalised), the Krylov basis is
-    orthonormalised, the matrix projected onto it and the small problem solved densely.  Stops when the
-    residuals |A v - w v| of the k wanted pairs are below tol * w_max.  Returns (w [k] descending, v [n, k]),
-    float64 on the device.  Small matrices are solved densely."""
+
+def _combine(u, s):
+    """u [n, m] times a small s [m, c] (conan_block_combine)."""
+    lib = _lib.load()
+    s = s.contiguous()
+    x = torch.empty((u.shape[0], s.shape[1]), dtype=torch.float64, device=u.device)
+    _lib.check(lib.conan_block_combine(u.data_ptr(), u.stride(0), u.shape[1], s.data_ptr(), s.shape[1], u.shape[0],
+                                       x.data_ptr(), x.stride(0), _stream(u.device)))
+    return x
+
+
+def _matvec(a32, w):
+    """a32 [n, n] float32 times w [n, b] float64, b <= 16 (conan_sym_block_matvec)."""
+    lib = _lib.load()
+    y = torch.empty_like(w)
+    _lib.check(lib.conan_sym_block_matvec(a32.data_ptr(), a32.stride(0), a32.shape[0], w.data_ptr(), w.stride(0), w.shape[1],
+                                          y.data_ptr(), y.stride(0), _stream(w.device)))
+    return y
+
+
+def _orthonormalise(w, against=None):
+    """Columns of w made orthonormal (and orthogonal to the orthonormal block `against`), through the small Gram
+    matrix: w <- w V L^-1/2 with G = w^T w = V L V^T; directions with an eigenvalue below 1e-24 of the largest
+    are dropped (the Krylov blocks lose rank as pairs converge).  Two passes, as Gram-based methods need."""
+    for _ in range(2):
+        if against is not None:
+            w = w - _combine(against, _gram(against, w))
+        lam, vec = torch.linalg.eigh(_gram(w, w))              # at most 16 x 16
+        keep = lam > 1.0e-24 * lam[-1].clamp_min(1.0e-300)
+        if not bool(keep.any()):
+            return w[:, :0]
+        w = _combine(w, vec[:, keep] / lam[keep].sqrt()[None, :])
+    return w
+
+
+def top_eigenpairs(cov, k, tol=1.0e-11, block_extra=6, depth=8, max_cycles=40, dense_below=2048):
+    """The k largest eigenpairs of a symmetric positive semi-definite float32 device matrix: eigsh(cov, k) of
+    conan.py:1985-1993 without factorising the whole matrix.
+
+    Restarted block Krylov iteration with Rayleigh-Ritz in float64.  Per cycle the block of Ritz vectors is
+    multiplied `depth` times by the matrix, every new block orthonormalised against all earlier ones; the
+    matrix is projected onto the basis and the small problem solved densely.  The products with the matrix
+    and with the tall blocks are this library's kernels (conan_sym_block_matvec / conan_block_gram /
+    conan_block_combine); only the dense problems of at most (depth + 1)(k + block_extra) unknowns go to a
+    library routine.  Stops when the residuals |A v - w v| of the k wanted pairs are below tol * w_max.
+    Returns (w [k] descending, v [n, k]), float64 on the device.  Small matrices are solved densely."""
     n = cov.shape[0]
     k = int(min(k, n))
-    if n <= dense_below or k + block_extra >= n // 4:
+    b = min(k + block_extra, 16)
+    if n <= dense_below or b >= n // 4 or (depth + 1) * b > 160 or k > b:
         w, v = torch.linalg.eigh(cov.double())
         return w.flip(0)[:k].contiguous(), v.flip(1)[:, :k].contiguous()
-    a = cov.double()
-    a = 0.5 * (a + a.T)
-    b = k + block_extra
+    a = cov if cov.dtype == torch.float32 and cov.is_contiguous() else cov.float().contiguous()
     gen = torch.Generator(device=cov.device)
     gen.manual_seed(20240229)
-    x = torch.randn((n, b), dtype=torch.float64, device=cov.device, generator=gen)
-    x, _ = torch.linalg.qr(x)
-    theta = None
+    x = _orthonormalise(torch.randn((n, b), dtype=torch.float64, device=cov.device, generator=gen))
+    theta = res = None
     for _ in range(max_cycles):
-        blocks = [x]
-        w_blk = x
+        blocks, prods = [x], []
+        basis = x
         for _ in range(depth):
-            w_blk, _ = torch.linalg.qr(a @ w_blk)
+            y = _matvec(a, blocks[-1])
+            prods.append(y)
+            w_blk = _orthonormalise(y, against=basis)
+            if w_blk.shape[1] == 0:
+                break
             blocks.append(w_blk)
-        q, _ = torch.linalg.qr(torch.cat(blocks, dim=1))
-        q, _ = torch.linalg.qr(q - q @ (q.T @ q - torch.eye(q.shape[1], dtype=q.dtype, device=q.device)))   # second pass
-        aq = a @ q
-        t = q.T @ aq
-        theta_all, s = torch.linalg.eigh(0.5 * (t + t.T))
-        s = s.flip(1)[:, :b]
-        theta = theta_all.flip(0)[:b]
-        x = q @ s
-        res = torch.linalg.vector_norm(aq @ s - x * theta[None, :], dim=0)
+            basis = torch.cat(blocks, dim=1)
+        if len(prods) < len(blocks):
+            prods.append(_matvec(a, blocks[-1]))
+        aq = torch.cat(prods, dim=1)                              # A times the basis, block by block
+        t = _gram(basis, aq)
+        theta_all, s = torch.linalg.eigh(0.5 * (t + t.T))         # at most 160 x 160
+        nb = min(b, s.shape[1])
+        s = s.flip(1)[:, :nb].contiguous()
+        theta = theta_all.flip(0)[:nb]
+        x = _combine(basis, s)
+        r = _combine(aq, s) - x * theta[None, :]
+        res = torch.sqrt(torch.diagonal(_gram(r, r)))
         if float(res[:k].max().item()) <= tol * float(theta[0].abs().item()):
             break
-        x, _ = torch.linalg.qr(x)
+        x = _orthonormalise(x)
     else:
         raise _lib.ConanError(-4, "top_eigenpairs did not converge (residual %.3g)" % float(res[:k].max().item()))
     return theta[:k].contiguous(), x[:, :k].contiguous()

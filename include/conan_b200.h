@@ -301,6 +301,22 @@ int conan_gemm_3xtf32(const uint16_t* d_a_hi, const uint16_t* d_a_lo, int32_t M,
                       const double* d_row_norm2, const double* d_col_norm2, int32_t symmetric, float* d_c,
                       int64_t ldc, void* stream);
 
+/* The block products of the top-k eigensolver that stands where the reference calls eigsh(covmat, k)
+ * (conan.py:1985-1993).  Blocks of vectors are float64 [n][ld] row-major.  K, M, N of
+ * conan_gemm_3xtf32 and all sizes here must fit 31 bits.
+ *   conan_sym_block_matvec   Y [n][b] = A W, A float32 [n][lda] (the covariance conan_gemm_3xtf32 wrote),
+ *                            b <= 16; float64 multiply-adds.  Reads A once: 4 n^2 bytes from HBM per product.
+ *   conan_block_gram         G [mu][mv] = U^T V (orthogonalisation and Rayleigh-Ritz), mu, mv <= 160
+ *   conan_block_combine      X [n][c] = U [n][m] S [m][c] (rotation of a basis by a small matrix), m, c <= 160,
+ *                            X must not alias U
+ */
+int conan_sym_block_matvec(const float* d_A, int64_t lda, int32_t n, const double* d_W, int64_t ldw, int32_t b,
+                           double* d_Y, int64_t ldy, void* stream);
+int conan_block_gram(const double* d_U, int64_t ldu, int32_t mu, const double* d_V, int64_t ldv, int32_t mv,
+                     int32_t n, double* d_G, void* stream);
+int conan_block_combine(const double* d_U, int64_t ldu, int32_t m, const double* d_S, int32_t c, int32_t n,
+                        double* d_X, int64_t ldx, void* stream);
+
 /* ------------------------------------------------------------------------------------ */
 /* Text writers of the file contract (host).  HOST pointers.         */
 /* ------------------------------------------------------------------------------------ */
