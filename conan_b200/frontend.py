@@ -334,13 +334,19 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     import torch
     from . import stage1
     from .xtc import XtcFile
-    if not traj.lower().endswith(".xtc"):
-        print("Only .xtc trajectories can be read without GROMACS; got %s" % traj)
-        sys.exit()
+    is_xtc = traj.lower().endswith(".xtc")
     nlevels = nlevels if nlevels else 40          # gmx mdmat defaults: -nlevels 40, -t 1.5
     trunc = trunc if trunc else 1.5
     top = topology.read_topology(coord)
-    x = XtcFile(traj)
+    if is_xtc:
+        x = XtcFile(traj)
+    else:       # .trr / multi-frame .gro / multi-model .pdb: plain numbers, read on the host (trajio.py)
+        from . import trajio
+        try:
+            x = trajio.open_trajectory(traj)
+        except ValueError as err:
+            print(err)
+            sys.exit()
     if x.natoms < top.natoms:
         top = top.truncated(x.natoms)
     elif x.natoms > top.natoms:
@@ -383,55 +389,82 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     counters = torch.zeros(3, dtype=torch.int64, device=dev)
     batch = max(1, min(len(frames), 2048))
     work = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
-    # The compressed frames go to the GPU as they are on disk and are decoded there (conan_xtc_decode_device).
-    # Two pinned staging buffers and a copy stream: the bytes of batch b+1 travel while batch b is decoded and
-    # its distances are computed; nothing waits on the host between batches.
-    lib = _lib.load()
-    spans = []
-    for b0 in range(0, len(frames), batch):
-        ids = frames[b0:b0 + batch]
-        lo, last = int(ids.min()), int(ids.max())
-        spans.append((b0, ids, int(x.offsets[lo]), int(x.offsets[last + 1]) if last + 1 < x.nframes else int(x._buf.size)))
-    max_bytes = max((s[3] - s[2] for s in spans), default=0)
-    h_stage = [torch.empty(max_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
-    h_off = [torch.empty(batch, dtype=torch.int64).pin_memory() for _ in range(2)]
-    d_stage = [torch.empty(max_bytes, dtype=torch.uint8, device=dev) for _ in range(2)]
-    d_off = [torch.empty(batch, dtype=torch.int64, device=dev) for _ in range(2)]
     d_coords = torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev)
-    d_status = torch.full((max(len(frames), 1),), -1, dtype=torch.int32, device=dev)
-    slot = np.full(x.natoms, -1, np.int32)
-    slot[np.asarray(sel, dtype=np.int64)] = np.arange(len(sel), dtype=np.int32)
-    d_slot = torch.from_numpy(slot).to(dev)
+    d_status = torch.zeros((max(len(frames), 1),), dtype=torch.int32, device=dev)
     d_boxes = torch.from_numpy(np.ascontiguousarray(boxes, dtype=np.float32).reshape(-1, 9)).to(dev) if use_pbc else None
     copy_stream = torch.cuda.Stream(dev)
     main_stream = torch.cuda.current_stream(dev)
     host_free = [None, None]      # event after the H2D copy that read each pinned buffer
-    dev_free = [None, None]       # event after the decode that read each device staging buffer
-    with torch.cuda.device(dev):
-        for n, (b0, ids, lo_b, hi_b) in enumerate(spans):
-            k = n % 2
-            if host_free[k] is not None:
-                host_free[k].synchronize()            # the pinned buffer is rewritten by the host below
-            nbytes = hi_b - lo_b
-            h_stage[k][:nbytes].numpy()[:] = x._buf[lo_b:hi_b]
-            h_off[k][:len(ids)].numpy()[:] = x.offsets[ids] - lo_b
-            with torch.cuda.stream(copy_stream):
-                if dev_free[k] is not None:
-                    copy_stream.wait_event(dev_free[k])
-                d_stage[k][:nbytes].copy_(h_stage[k][:nbytes], non_blocking=True)
-                d_off[k][:len(ids)].copy_(h_off[k][:len(ids)], non_blocking=True)
-                copied = torch.cuda.Event()
-                copied.record(copy_stream)
-            host_free[k] = copied
-            main_stream.wait_event(copied)
-            _lib.check(lib.conan_xtc_decode_device(d_stage[k].data_ptr(), nbytes, d_off[k].data_ptr(), len(ids), x.natoms,
-                                                   d_slot.data_ptr(), len(sel), d_coords.data_ptr(),
-                                                   d_status[b0:b0 + len(ids)].data_ptr(), main_stream.cuda_stream))
-            decoded = torch.cuda.Event()
-            decoded.record(main_stream)
-            dev_free[k] = decoded
-            stage1.mdmat_frames(d_coords[:len(ids)], None if d_boxes is None else d_boxes[b0:b0 + len(ids)], geom, trunc,
-                                nlevels, use_pbc, levels[b0:b0 + len(ids)], work, counters)
+    dev_free = [None, None]       # event after the kernel that read each device staging buffer
+    if is_xtc:
+        # The compressed frames go to the GPU as they are on disk and are decoded there (conan_xtc_decode_device).
+        # Two pinned staging buffers and a copy stream: the bytes of batch b+1 travel while batch b is decoded and
+        # its distances are computed; nothing waits on the host between batches.
+        lib = _lib.load()
+        spans = []
+        for b0 in range(0, len(frames), batch):
+            ids = frames[b0:b0 + batch]
+            lo, last = int(ids.min()), int(ids.max())
+            spans.append((b0, ids, int(x.offsets[lo]), int(x.offsets[last + 1]) if last + 1 < x.nframes else int(x._buf.size)))
+        max_bytes = max((sp[3] - sp[2] for sp in spans), default=0)
+        h_stage = [torch.empty(max_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        h_off = [torch.empty(batch, dtype=torch.int64).pin_memory() for _ in range(2)]
+        d_stage = [torch.empty(max_bytes, dtype=torch.uint8, device=dev) for _ in range(2)]
+        d_off = [torch.empty(batch, dtype=torch.int64, device=dev) for _ in range(2)]
+        d_status.fill_(-1)
+        slot = np.full(x.natoms, -1, np.int32)
+        slot[np.asarray(sel, dtype=np.int64)] = np.arange(len(sel), dtype=np.int32)
+        d_slot = torch.from_numpy(slot).to(dev)
+        with torch.cuda.device(dev):
+            for n, (b0, ids, lo_b, hi_b) in enumerate(spans):
+                k = n % 2
+                if host_free[k] is not None:
+                    host_free[k].synchronize()            # the pinned buffer is rewritten by the host below
+                nbytes = hi_b - lo_b
+                h_stage[k][:nbytes].numpy()[:] = x._buf[lo_b:hi_b]
+                h_off[k][:len(ids)].numpy()[:] = x.offsets[ids] - lo_b
+                with torch.cuda.stream(copy_stream):
+                    if dev_free[k] is not None:
+                        copy_stream.wait_event(dev_free[k])
+                    d_stage[k][:nbytes].copy_(h_stage[k][:nbytes], non_blocking=True)
+                    d_off[k][:len(ids)].copy_(h_off[k][:len(ids)], non_blocking=True)
+                    copied = torch.cuda.Event()
+                    copied.record(copy_stream)
+                host_free[k] = copied
+                main_stream.wait_event(copied)
+                _lib.check(lib.conan_xtc_decode_device(d_stage[k].data_ptr(), nbytes, d_off[k].data_ptr(), len(ids), x.natoms,
+                                                       d_slot.data_ptr(), len(sel), d_coords.data_ptr(),
+                                                       d_status[b0:b0 + len(ids)].data_ptr(), main_stream.cuda_stream))
+                decoded = torch.cuda.Event()
+                decoded.record(main_stream)
+                dev_free[k] = decoded
+                stage1.mdmat_frames(d_coords[:len(ids)], None if d_boxes is None else d_boxes[b0:b0 + len(ids)], geom, trunc,
+                                    nlevels, use_pbc, levels[b0:b0 + len(ids)], work, counters)
+    else:
+        # plain coordinates: the index group's atoms of a batch are gathered into a pinned buffer and copied on
+        # the copy stream while the batch before is computed
+        h_xyz = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32).pin_memory() for _ in range(2)]
+        d_xyz = [d_coords, torch.empty_like(d_coords)]
+        with torch.cuda.device(dev):
+            for n, b0 in enumerate(range(0, len(frames), batch)):
+                ids = frames[b0:b0 + batch]
+                k = n % 2
+                if host_free[k] is not None:
+                    host_free[k].synchronize()
+                h_xyz[k][:len(ids)].numpy()[:] = x.coords(ids, sel)
+                with torch.cuda.stream(copy_stream):
+                    if dev_free[k] is not None:
+                        copy_stream.wait_event(dev_free[k])
+                    d_xyz[k][:len(ids)].copy_(h_xyz[k][:len(ids)], non_blocking=True)
+                    copied = torch.cuda.Event()
+                    copied.record(copy_stream)
+                host_free[k] = copied
+                main_stream.wait_event(copied)
+                stage1.mdmat_frames(d_xyz[k][:len(ids)], None if d_boxes is None else d_boxes[b0:b0 + len(ids)], geom, trunc,
+                                    nlevels, use_pbc, levels[b0:b0 + len(ids)], work, counters)
+                done = torch.cuda.Event()
+                done.record(main_stream)
+                dev_free[k] = done
     torch.cuda.synchronize(dev)
     bad = torch.nonzero(d_status[:len(frames)]).flatten()
     if bad.numel():

@@ -233,3 +233,54 @@ def test_command_line_on_two_ranks_equals_one(lib, tmp_path):
                  "cluster_trj/2/assignment.dat", "cluster_trj/rmsd_interframe.dat"):
         a, b = np.loadtxt(str(one / name)), np.loadtxt(str(two / name))
         assert np.array_equal(a, b), name
+
+
+def test_other_trajectory_formats_give_the_same_matrices(lib, tmp_path):
+    """The reference's peptide trajectory rewritten as .trr (float and double), multi-frame .gro and multi-model
+    .pdb: `conan.py` produces the same matrices and tables as from the .xtc (docs/index.md:143-149: whatever gmx
+    reads).  The coordinates have three decimals, which every one of these formats keeps exactly."""
+    from conan_b200 import topology, trajio
+    from conan_b200.xtc import XtcFile
+    x = XtcFile(os.path.join(GOLDEN, "sample.xtc"))
+    xyz = x.decode()
+    top = topology.read_gro(os.path.join(GOLDEN, "peptide.gro"))
+    box = x.boxes
+    files = {}
+    files["trr"] = str(tmp_path / "t.trr")
+    trajio.write_trr(files["trr"], xyz, box, x.times)
+    files["trr64"] = str(tmp_path / "t64.trr")
+    trajio.write_trr(files["trr64"], xyz.astype(np.float64), box, x.times, double=True)
+    files["gro"] = str(tmp_path / "t.gro")
+    with open(files["gro"], "w") as f:
+        for k in range(len(xyz)):
+            f.write("frame t= %.5f\n%5d\n" % (x.times[k], top.natoms))
+            for a in range(top.natoms):
+                f.write("%5d%-5s%5s%5d%8.3f%8.3f%8.3f\n" % (top.resids[a] % 100000, top.resnames[a][:5], top.names[a][:5], (a + 1) % 100000,
+                                                           xyz[k, a, 0], xyz[k, a, 1], xyz[k, a, 2]))
+            f.write("%10.5f%10.5f%10.5f\n" % (box[k, 0, 0], box[k, 1, 1], box[k, 2, 2]))
+    files["pdb"] = str(tmp_path / "t.pdb")
+    with open(files["pdb"], "w") as f:
+        for k in range(len(xyz)):
+            f.write("CRYST1%9.3f%9.3f%9.3f%7.2f%7.2f%7.2f P 1           1\nMODEL     %4d\n"
+                    % (10 * box[k, 0, 0], 10 * box[k, 1, 1], 10 * box[k, 2, 2], 90, 90, 90, k + 1))
+            for a in range(top.natoms):
+                f.write("ATOM  %5d %-4s %-3s %1s%4d    %8.3f%8.3f%8.3f  1.00  0.00\n"
+                        % ((a + 1) % 100000, top.names[a][:4], top.resnames[a][:3], "A", top.resids[a] % 10000,
+                           10 * xyz[k, a, 0], 10 * xyz[k, a, 1], 10 * xyz[k, a, 2]))
+            f.write("TER\nENDMDL\n")
+    ref = tmp_path / "xtc"
+    ref.mkdir()
+    base = "COORD %s/peptide.gro\nTRUNC 1.0\nNLEVEL 1001\nMAKE_MOVIE no\n" % GOLDEN
+    _run_cli(str(ref), "TRAJ %s/sample.xtc\n" % GOLDEN + base)
+    for tag, path in files.items():
+        d = tmp_path / tag
+        d.mkdir()
+        _run_cli(str(d), "TRAJ %s\n" % path + base)
+        for name in ("matrices/00000.dat", "matrices/00007.dat", "aggregate/mdmat_average_rmsf.dat", "aggregate/native_contacts.dat"):
+            a, b = np.loadtxt(str(ref / name)), np.loadtxt(str(d / name))
+            if tag == "pdb" and "native" in name:
+                a, b = a[:, 1:], b[:, 1:]                                  # .pdb models carry no times
+            assert np.array_equal(a, b), (tag, name)
+        tl_a, tl_b = np.loadtxt(str(ref / "aggregate/timeline.dat")), np.loadtxt(str(d / "aggregate/timeline.dat"))
+        cols = [0, 1, 4, 6] if tag == "pdb" else [0, 1, 2, 3, 4, 6]          # .pdb models carry no times
+        assert np.array_equal(tl_a[:, cols], tl_b[:, cols]), tag
