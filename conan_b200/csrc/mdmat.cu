@@ -837,7 +837,8 @@ size_t mdmat_smem_bytes(int kpad, int fb) {
 // (six frames per CTA at eight atoms per residue); 1: 256 threads x 3 CTAs per SM, 80 registers and 74 KB
 // (three frames).  The first is faster (18.0 against 20.0 ms per 12 500 frames of 1000 residues): the tile
 // kernel does not fit 80 registers without spilling in its item loop, and twice the frames per CTA halve
-// the set-up and pruning work per frame.
+// the set-up and pruning work per frame.  More, thinner warps do not pay either: 320 threads x 2 (96
+// registers) 19.2 ms, 384 x 2 (80 registers) 20.7 ms, 128 x 4 (128 registers, two frames) 20.8 ms.
 struct CtaShape { int threads, per_sm; size_t budget; };
 inline CtaShape cta_shape(int cfg) {
     if (cfg == 1) return CtaShape{256, 3, (size_t)74 * 1024};
