@@ -201,11 +201,11 @@ def _orthonormalise(w, against=None):
     for _ in range(2):
         if against is not None:
             w = w - _combine(against, _gram(against, w))
-        lam, vec = torch.linalg.eigh(_gram(w, w))              # at most 16 x 16
-        keep = lam > 1.0e-24 * lam[-1].clamp_min(1.0e-300)
-        if not bool(keep.any()):
+        lam, vec = np.linalg.eigh(_gram(w, w).cpu().numpy())   # at most 16 x 16: solved on the host
+        keep = lam > 1.0e-24 * max(lam[-1], 1.0e-300)
+        if not keep.any():
             return w[:, :0]
-        w = _combine(w, vec[:, keep] / lam[keep].sqrt()[None, :])
+        w = _combine(w, torch.from_numpy(np.ascontiguousarray(vec[:, keep] / np.sqrt(lam[keep])[None, :])).to(w.device))
     return w
 
 
@@ -217,8 +217,8 @@ def top_eigenpairs(cov, k, tol=1.0e-11, block_extra=6, depth=8, max_cycles=40, d
     multiplied `depth` times by the matrix, every new block orthonormalised against all earlier ones; the
     matrix is projected onto the basis and the small problem solved densely.  The products with the matrix
     and with the tall blocks are this library's kernels (conan_sym_block_matvec / conan_block_gram /
-    conan_block_combine); only the dense problems of at most (depth + 1)(k + block_extra) unknowns go to a
-    library routine.  Stops when the residuals |A v - w v| of the k wanted pairs are below tol * w_max.
+    conan_block_combine); the dense problems of at most (depth + 1)(k + block_extra) <= 160 unknowns in between
+    are solved on the host (LAPACK through numpy, microseconds).  Stops when the residuals |A v - w v| of the k wanted pairs are below tol * w_max.
     Returns (w [k] descending, v [n, k]), float64 on the device.  Small matrices are solved densely."""
     n = cov.shape[0]
     k = int(min(k, n))
@@ -245,11 +245,11 @@ def top_eigenpairs(cov, k, tol=1.0e-11, block_extra=6, depth=8, max_cycles=40, d
         if len(prods) < len(blocks):
             prods.append(_matvec(a, blocks[-1]))
         aq = torch.cat(prods, dim=1)                              # A times the basis, block by block
-        t = _gram(basis, aq)
-        theta_all, s = torch.linalg.eigh(0.5 * (t + t.T))         # at most 160 x 160
+        t = _gram(basis, aq).cpu().numpy()
+        theta_all, s = np.linalg.eigh(0.5 * (t + t.T))             # at most 160 x 160: solved on the host
         nb = min(b, s.shape[1])
-        s = s.flip(1)[:, :nb].contiguous()
-        theta = theta_all.flip(0)[:nb]
+        s = torch.from_numpy(np.ascontiguousarray(s[:, ::-1][:, :nb])).to(cov.device)
+        theta = torch.from_numpy(np.ascontiguousarray(theta_all[::-1][:nb])).to(cov.device)
         x = _combine(basis, s)
         r = _combine(aq, s) - x * theta[None, :]
         res = torch.sqrt(torch.diagonal(_gram(r, r)))

@@ -143,10 +143,15 @@ int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int64_t nf, in
  * CONAN_MDMAT_STATIC_SCRATCH_BYTES array inside the library (resident on every GPU that loads
  * the library, until the process exits), so a call is limited to as many frames as
  *     conan_mdmat_workspace_bytes(nf, natoms, nres, max_res_atoms) <= CONAN_MDMAT_STATIC_SCRATCH_BYTES
- * allows (about 135 frames of a 1000-residue, 8-atoms-per-residue system); larger calls return
+ * allows (about 225 frames of a 1000-residue, 8-atoms-per-residue system); larger calls return
  * CONAN_ERR_SIZE and must be split.  It calls no cudaMalloc, cudaFree or other allocating routine.
- * The first call on each device looks up the array's device address; make that first call
- * before starting any stream capture.  All calls on a device share the one array, which keeps the
+ * The first call on each device does the set-up: it looks up the array's device address, raises the
+ * shared-memory limit of the tile kernels and makes the runtime load every kernel the call can reach
+ * (the periodic and the non-periodic variant, all residue-size variants), so that later calls load no
+ * code either; make that first call before the step loop and before starting any stream capture.
+ * h_res_start is copied to the device with cudaMemcpyAsync on every call: pass pinned host memory if the
+ * call must not wait for the stream, and keep it alive until the stream has consumed it.
+ * All calls on a device share the one array, which keeps the
  * previous call's contents (nothing in it needs to start at zero: each call rewrites what it
  * reads); two calls whose GPU work overlaps -- different streams, or different host threads --
  * race on it, so issue them on one stream or otherwise order them.
