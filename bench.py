@@ -60,6 +60,7 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU, help="frames per GPU")
     ap.add_argument("--nres", type=int, default=NRES)
     ap.add_argument("--batch", type=int, default=1250, help="frames per H2D batch of the e2e leg")
+    ap.add_argument("--e2e-batches", type=int, default=3, help="batches of the e2e leg: the first of --batch frames, the rest equal")
     ap.add_argument("--cpu-frames", type=int, default=48, help="frames of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stage3", action="store_true", help="skip the stage-3 (Pearson / covariance / frame-frame) leg")
@@ -328,15 +329,14 @@ def run_ours(args):
     # ---- end to end from host memory: the shard's .xtc bytes in, the statistics out -----------------------
     from concurrent.futures import ThreadPoolExecutor
     from conan_b200.xtc import XtcFile, encode_xtc
-    # The decoder works a warp per frame and is bound by the length of a frame's chain, not by the GPU: a launch
-    # takes about a millisecond however few frames it has, and it cannot run beside the distance kernel (whose
-    # CTAs hold the whole register file).  So the shard goes in few, large batches: a first one of --batch frames
-    # that gets the pipeline going, the rest in two halves.
+    # A decode launch is bound by the length of one frame's flag walk (a few tenths of a millisecond however few
+    # frames it has), and it finds little room beside the distance kernel (whose CTAs hold the whole register
+    # file).  So the shard goes in few, large batches: a first one of --batch frames that gets the pipeline going,
+    # the rest in two halves.
     first = max(1, min(args.batch, nf))
-    edges = [0, first]
-    if first < nf:
-        edges += [first + (nf - first + 1) // 2, nf] if nf - first > 1 else [nf]
-    edges = sorted(set(edges))
+    rest = max(1, args.e2e_batches - 1)
+    edges = [0, first] + [first + ((nf - first) * q + rest - 1) // rest for q in range(1, rest + 1)]
+    edges = sorted(set(min(e, nf) for e in edges))
     nb = len(edges) - 1
     batch = max(edges[b + 1] - edges[b] for b in range(nb))
     def encode(b):      # one .xtc stream per batch (what a trajectory file split at those frames would hold)
@@ -354,7 +354,10 @@ def run_ours(args):
     d_coords = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(2)]
     d_status = torch.zeros(nf, dtype=torch.int32, device=dev)
     work_b = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
-    copy_stream, dec_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    # scratch of the two-pass decoder (one buffer: the decodes follow each other on one stream)
+    dec_work = torch.empty(int(lib.conan_xtc_decode_workspace_bytes(batch, geom.natoms)), dtype=torch.uint8, device=dev)
+    copy_stream, dec_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev, priority=-1)
+    d2h_stream = torch.cuda.Stream(dev)
     host_out = {n: torch.empty(getattr(out, n).shape, dtype=getattr(out, n).dtype).pin_memory()
                 for n, _ in stage2.PairStats.PAIR_FIELDS + stage2.PairStats.FRAME_FIELDS}
     d2h_bytes = sum(t.numel() * t.element_size() for t in host_out.values())
@@ -381,9 +384,10 @@ def run_ours(args):
                 dec_stream.wait_event(copied)
                 if coords_free[c] is not None:
                     dec_stream.wait_event(coords_free[c])
-                _lib.check(lib.conan_xtc_decode_device(stage_buf[k].data_ptr(), h_bytes[b].numel(), stage_off[k].data_ptr(), b1 - b0,
-                                                       geom.natoms, None, geom.natoms, d_coords[c].data_ptr(),
-                                                       d_status[b0:b1].data_ptr(), dec_stream.cuda_stream))
+                _lib.check(lib.conan_xtc_decode_device_ws(stage_buf[k].data_ptr(), h_bytes[b].numel(), stage_off[k].data_ptr(), b1 - b0,
+                                                          geom.natoms, None, geom.natoms, d_coords[c].data_ptr(),
+                                                          d_status[b0:b1].data_ptr(), dec_work.data_ptr(), dec_work.numel(),
+                                                          dec_stream.cuda_stream))
                 decoded = torch.cuda.Event()
                 decoded.record(dec_stream)
             bytes_free[k] = decoded
@@ -392,13 +396,24 @@ def run_ours(args):
             done = torch.cuda.Event()
             done.record(stream)
             coords_free[c] = done
+        if results_home[0] is not None:
+            stream.wait_event(results_home[0])      # the previous step's results have left `out`
         if world > 1:
             sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
         else:
             stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2)
-        for n in host_out:
-            host_out[n].copy_(getattr(out, n), non_blocking=True)
+        # the results go home on a stream of their own, so the next step's kernels do not queue behind the transfer
+        computed = torch.cuda.Event()
+        computed.record(stream)
+        with torch.cuda.stream(d2h_stream):
+            d2h_stream.wait_event(computed)
+            for n in host_out:
+                host_out[n].copy_(getattr(out, n), non_blocking=True)
+            fetched = torch.cuda.Event()
+            fetched.record(d2h_stream)
+        results_home[0] = fetched
 
+    results_home = [None]
     for _ in range(2):
         step_e2e()
     barrier()
@@ -407,6 +422,7 @@ def run_ours(args):
     a.record(stream)
     for _ in range(args.steps):
         step_e2e()
+    stream.wait_event(results_home[0])          # the timed region ends when the last step's results are on the host
     b.record(stream)
     barrier()
     ms_e2e = a.elapsed_time(b)
@@ -516,7 +532,14 @@ def run_xtc_feed(args, dev, xyz):
     d_status = torch.zeros(n, dtype=torch.int32, device=dev)
     stream = torch.cuda.current_stream(dev)
 
+    d_work = torch.empty(int(lib.conan_xtc_decode_workspace_bytes(n, natoms)), dtype=torch.uint8, device=dev)
+
     def decode():
+        _lib.check(lib.conan_xtc_decode_device_ws(d_data.data_ptr(), d_data.numel(), d_off.data_ptr(), n, natoms, None, natoms,
+                                                  d_out.data_ptr(), d_status.data_ptr(), d_work.data_ptr(), d_work.numel(),
+                                                  stream.cuda_stream))
+
+    def decode_one_pass():
         _lib.check(lib.conan_xtc_decode_device(d_data.data_ptr(), d_data.numel(), d_off.data_ptr(), n, natoms, None, natoms,
                                                d_out.data_ptr(), d_status.data_ptr(), stream.cuda_stream))
 
@@ -532,7 +555,12 @@ def run_xtc_feed(args, dev, xyz):
         return a.elapsed_time(b) / reps
 
     d_data.copy_(h_data)
+    ms_one_pass = timed(decode_one_pass)
+    one_pass_out = d_out.clone()
+    d_out.zero_()
     ms_kernel = timed(decode)
+    same_decoders = bool(torch.equal(one_pass_out, d_out))
+    del one_pass_out
 
     def feed():
         d_data.copy_(h_data, non_blocking=True)
@@ -547,7 +575,11 @@ def run_xtc_feed(args, dev, xyz):
     same = bool(np.array_equal(d_out.cpu().numpy(), host))
     os.remove(path)
     return {"workload": "first %d frames of the shard as .xtc (%d atoms, %.2f bytes per atom)" % (n, natoms, nbytes / n / natoms),
-            "kernel": "xtc_decode_kernel", "decode_ms": ms_kernel, "atoms_per_s": n * natoms / (ms_kernel * 1e-3),
+            "kernel": "xtc_walk_kernel + xtc_groups_kernel (conan_xtc_decode_device_ws)", "decode_ms": ms_kernel,
+            "atoms_per_s": n * natoms / (ms_kernel * 1e-3),
+            "one_pass": {"kernel": "xtc_decode_kernel (conan_xtc_decode_device)", "decode_ms": ms_one_pass,
+                         "atoms_per_s": n * natoms / (ms_one_pass * 1e-3), "same_coordinates": same_decoders},
+            "scratch_bytes": int(d_work.numel()),
             "h2d_plus_decode_ms": ms_feed, "compressed_bytes": int(nbytes), "float_bytes": int(n * natoms * 12),
             "host_decode": {"ms": t_host * 1e3, "threads": threads, "atoms_per_s": n * natoms / t_host},
             "bit_identical_to_host_decoder": same}

@@ -10,6 +10,8 @@
 // in xtc.cpp, so the coordinates are bit-identical.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+#include <atomic>
 #include <cstdint>
 
 #include "common.h"
@@ -331,6 +333,341 @@ __global__ void __launch_bounds__(kDecodeThreads, 8) xtc_decode_kernel(const Dec
     finish(bad);
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Two passes (conan_xtc_decode_device_ws).  The walk over the run flags is a chain of a few integer
+// operations per group; done by a whole warp for one frame it occupies an issue slot per step for one
+// lane's worth of work.  Here pass 1 gives every frame one THREAD (32 frames share an issue slot), which
+// writes one 8-byte descriptor per group -- bit position, first atom, number of small codes and their
+// width -- and a record with the frame's header values; pass 2 decodes the groups, one per thread, with
+// as many warps per frame as the frame has groups.  Same integer arithmetic, same coordinates.
+// ------------------------------------------------------------------------------------------
+constexpr int kMaxWsAtoms = 1 << 21;      // `first` has 21 bits in a descriptor
+constexpr int kGroupThreads = 128;
+constexpr int kGroupsPerCta = 512;
+
+struct __align__(16) FrameRec {
+    int64_t stream_off;      // byte offset of the code stream inside d_data
+    uint64_t rcp1, rcp2;
+    uint32_t stream_bytes;   // its length, padded to 4
+    int32_t ngroups;         // 0: nothing for pass 2 (bad header, or a frame of plain floats written by pass 1)
+    int32_t minint[3];
+    uint32_t sizeint[3];
+    int32_t bitsint[3];
+    int32_t bitsize;
+    int32_t big_fast;
+    float inv;
+    int32_t pad[2];
+};
+static_assert(sizeof(FrameRec) % 16 == 0, "FrameRec is read with aligned loads");
+
+struct WalkParams {
+    DecodeParams d;
+    FrameRec* rec;           // [nframes]
+    uint2* desc;             // [nframes][natoms]
+};
+
+constexpr int kWalkWindow = 256;        // words of every frame's stream held in shared memory by the walk
+constexpr int kWalkWarps = 3;           // warps (of 32 frames) per CTA: few, fat CTAs, because a walk CTA that lands on an SM
+                                        // beside the distance kernel keeps one of that kernel's two CTAs out while it runs
+constexpr int kWalkSteps = 4;           // groups per round of the walk
+// words a lane may advance in one round before its reads leave the window: a group is at most 96 + 6 + 10 x 72 bits
+constexpr int kWalkMargin = ((kWalkSteps - 1) * (96 + 6 + 10 * 72) + 31) / 32 + 2;
+constexpr size_t kWalkSmem = (size_t)kWalkWarps * 32 * (kWalkWindow + 1) * sizeof(uint32_t);
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// c_rcp_magic[k] = ceil(2^32 / c_magic[k]): mulhi(v, m) is v / size or one more for every v < 2^32
+__constant__ uint32_t c_rcp_magic[kNumMagic] = {
+    0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u,
+    0u, 536870912u, 429496730u, 357913942u, 268435456u, 214748365u, 171798692u, 134217728u,
+    107374183u, 85899346u, 67108864u, 53687092u, 42524429u, 33554432u, 26676816u, 21157475u,
+    16777216u, 13338408u, 10578738u, 8388608u, 6658865u, 5289369u, 4194304u, 3329433u,
+    2643057u, 2097152u, 1664717u, 1321529u, 1048576u, 848808u, 660663u, 524288u,
+    416139u, 330306u, 262144u, 208070u, 165147u, 131072u, 104033u, 82572u,
+    65536u, 52017u, 41286u, 32768u, 26009u, 20643u, 16384u, 13005u,
+    10322u, 8193u, 6502u, 5161u, 4096u, 3251u, 2581u, 2048u,
+    1626u, 1291u, 1024u, 813u, 646u, 513u, 407u, 323u,
+    256u};
+
+__global__ void __launch_bounds__(32 * kWalkWarps) xtc_walk_kernel(const WalkParams wp) {
+    // the next kWalkWindow words of each of the warp's 32 streams (already in host byte order, zeros past the
+    // end), refilled for all lanes with coalesced loads whenever one lane reaches the end of its window:
+    // the chain below then depends on shared-memory reads, not on 32 scattered global loads of which one
+    // misses the L1 in nearly every step
+    extern __shared__ uint32_t win_all[];      // [kWalkWarps][32][kWalkWindow + 1]; the warps work on their own
+    uint32_t* win = win_all + (size_t)(threadIdx.x >> 5) * 32 * (kWalkWindow + 1);
+    const DecodeParams& prm = wp.d;
+    const int lane = threadIdx.x & 31;
+    const int64_t f = (int64_t)blockIdx.x * (32 * kWalkWarps) + threadIdx.x;
+    const int natoms = prm.natoms;
+    FrameRec r;
+    r.ngroups = 0;
+    int bad = kOk, smallidx = 0, bigbits = 0;
+    bool active = false;
+    const uint32_t* words = nullptr;
+    uint32_t nwords = 0;
+    if (f < prm.nframes) {
+        // (one pass through this do-block; `break` leaves it with `bad` set)
+        do {
+            const int64_t off = prm.offsets[f];
+            bad = kBadHeader;
+            if (off < 0 || (off & 3) || off + 56 > prm.nbytes) break;
+            const uint8_t* p = prm.data + off;
+            if ((int)load_be32(p) != 1995 || (int)load_be32(p + 4) != natoms) break;
+            const uint8_t* q = p + 56;
+            if (natoms <= 9) {   // stored as plain floats
+                if (off + 56 + (int64_t)natoms * 12 > prm.nbytes) break;
+                float* out = prm.xyz + (size_t)f * prm.nsel * 3;
+                for (int a = 0; a < natoms; a++) {
+                    const int sl = prm.slot ? prm.slot[a] : a;
+                    if (sl >= 0 && sl < prm.nsel)
+                        for (int d = 0; d < 3; d++) out[3 * (size_t)sl + d] = __uint_as_float(load_be32(q + 12 * a + 4 * d));
+                }
+                bad = kOk;
+                break;
+            }
+            if (off + 92 > prm.nbytes) break;
+            const float precision = __uint_as_float(load_be32(q));
+            for (int d = 0; d < 3; d++) {
+                r.minint[d] = (int32_t)load_be32(q + 4 + 4 * d);
+                r.sizeint[d] = (uint32_t)((int32_t)load_be32(q + 16 + 4 * d) - r.minint[d] + 1);
+            }
+            smallidx = (int32_t)load_be32(q + 28);
+            const int32_t nb = (int32_t)load_be32(q + 32);
+            if (smallidx < kFirstIdx || smallidx >= kNumMagic) { bad = kBadSmallIdx; break; }
+            if (nb < 0 || off + 92 + (((int64_t)nb + 3) & ~(int64_t)3) > prm.nbytes) break;
+            r.bitsint[0] = r.bitsint[1] = r.bitsint[2] = 0;
+            r.bitsize = 0;
+            if ((r.sizeint[0] | r.sizeint[1] | r.sizeint[2]) > 0xffffffu) {
+                for (int d = 0; d < 3; d++) r.bitsint[d] = bits_for(r.sizeint[d]);
+                bigbits = r.bitsint[0] + r.bitsint[1] + r.bitsint[2];
+            } else {
+                const uint64_t p01 = (uint64_t)r.sizeint[0] * r.sizeint[1];
+                const uint64_t lo = p01 * r.sizeint[2], hi = __umul64hi(p01, (uint64_t)r.sizeint[2]);
+                r.bitsize = hi ? 128 - __clzll((long long)hi) : (lo ? 64 - __clzll((long long)lo) : 0);
+                bigbits = r.bitsize;
+            }
+            r.big_fast = r.bitsize > 0 && r.bitsize <= 64 && r.sizeint[1] >= 2 && r.sizeint[2] >= 2;
+            r.rcp1 = r.rcp2 = 0;
+            if (r.big_fast) { r.rcp1 = ~0ull / r.sizeint[1] + 1; r.rcp2 = ~0ull / r.sizeint[2] + 1; }
+            const uint8_t* sbase = q + 36;
+            const uint32_t sbytes = (uint32_t)(((size_t)nb + 3) & ~(size_t)3);
+            r.stream_off = (int64_t)(sbase - prm.data);
+            r.stream_bytes = sbytes;
+            r.inv = __fdiv_rn(1.0f, precision);
+            r.pad[0] = r.pad[1] = 0;
+            words = reinterpret_cast<const uint32_t*>(sbase);
+            nwords = sbytes >> 2;
+            bad = kOk;
+            active = true;
+        } while (false);
+    }
+
+    // the chain: position -> six bits behind the full-size code -> run length / code width -> next position.
+    // Written without branches (a lane that is done idles under its predicate) and in rounds of kWalkSteps
+    // groups, so the warp votes once per round: is a refill due, is anyone still walking.
+    uint2* desc = wp.desc + (size_t)(f < prm.nframes ? f : 0) * natoms;
+    uint32_t* mywin = win + (size_t)lane * (kWalkWindow + 1);
+    uint32_t pos = 0, base = 0;
+    bool filled = false;
+    int ns = 0, i = 0, g = 0;
+    const uint32_t nw_eff = active ? nwords : 0u;
+    const uint32_t wlo = (uint32_t)reinterpret_cast<uintptr_t>(words), whi = (uint32_t)(reinterpret_cast<uintptr_t>(words) >> 32);
+    while (__any_sync(0xffffffffu, active)) {
+        const uint32_t w_now = (pos + (uint32_t)bigbits) >> 5;
+        const bool need = active && (!filled || w_now + 1 + kWalkMargin - base >= (uint32_t)kWalkWindow);
+        if (__any_sync(0xffffffffu, need)) {
+            // all 32 windows restart at their lane's position: asynchronous 4-byte copies straight into shared
+            // memory (zeros past the end of a stream), one wait for all of them
+            if (active) base = w_now;
+            __syncwarp();
+#pragma unroll 2
+            for (int k = 0; k < 32; k++) {
+                const uint32_t nk = __shfl_sync(0xffffffffu, nw_eff, k), bk = __shfl_sync(0xffffffffu, base, k);
+                const uint32_t lo = __shfl_sync(0xffffffffu, wlo, k), hi = __shfl_sync(0xffffffffu, whi, k);
+                if (nk == 0) continue;
+                const uint32_t* wk = reinterpret_cast<const uint32_t*>(((uintptr_t)hi << 32) | lo);
+                const uint32_t dst = smem_u32(win + (size_t)k * (kWalkWindow + 1) + lane);
+#pragma unroll
+                for (int j = 0; j < kWalkWindow / 32; j++) {
+                    const uint32_t idx = bk + 32 * j + lane;
+                    const bool in = idx < nk;
+                    cp_async4(dst + 128u * j, wk + (in ? idx : 0u), in ? 4u : 0u);
+                }
+            }
+            cp_async_wait_all();
+            __syncwarp();
+            filled = true;
+        }
+#pragma unroll
+        for (int u = 0; u < kWalkSteps; u++) {
+            const uint32_t at = pos + (uint32_t)bigbits;
+            const uint32_t rel = (at >> 5) - base;
+            const uint32_t w0 = __byte_perm(mywin[rel], 0, 0x0123), w1 = __byte_perm(mywin[rel + 1], 0, 0x0123);
+            const uint32_t six = __funnelshift_l(w1, w0, (int)(at & 31)) >> 26;
+            const bool flag = (six >> 5) != 0;
+            const int r5 = (int)(six & 31u);
+            const int q3 = (r5 * 11) >> 5;                  // r5 / 3 for r5 < 32
+            const int sm = r5 - 3 * q3;
+            ns = flag ? q3 : ns;                            // number of small codes of this and the following groups
+            const int d_idx = flag ? sm - 1 : 0;
+            const bool fits = !(ns > 0 && i + 1 + ns > natoms);
+            const bool ok = active && fits;
+            if (ok) desc[g] = make_uint2(pos, (uint32_t)i | ((uint32_t)ns << 21) | ((uint32_t)smallidx << 25));
+            if (active && !fits) bad = kRunPastEnd;
+            g += ok ? 1 : 0;
+            pos += ok ? (uint32_t)(bigbits + (flag ? 6 : 1) + ns * smallidx) : 0u;
+            i += ok ? 1 + ns : 0;
+            smallidx += ok ? d_idx : 0;
+            const bool idx_bad = smallidx < kFirstIdx || smallidx >= kNumMagic;
+            if (ok && idx_bad) bad = kBadSmallIdx;
+            active = ok && !idx_bad && i < natoms;
+        }
+    }
+    if (f < prm.nframes) {
+        if (nwords && (uint64_t)pos > (uint64_t)nwords * 32 && bad == kOk) bad = kStreamPastEnd;
+        r.ngroups = g;        // groups confirmed before a fault are still decoded (the reader pads with zeros)
+        prm.status[f] = bad;
+        wp.rec[f] = r;
+    }
+}
+
+// 64 bits of the stream from bit `pos` on (big-endian bit order, zeros past the end)
+__device__ __forceinline__ uint64_t peek64(const uint32_t* __restrict__ words, uint32_t nwords, uint32_t pos) {
+    const uint32_t w = pos >> 5;
+    const int sh = (int)(pos & 31);
+    const uint32_t a = w < nwords ? __byte_perm(__ldg(words + w), 0, 0x0123) : 0u;
+    const uint32_t b = w + 1 < nwords ? __byte_perm(__ldg(words + w + 1), 0, 0x0123) : 0u;
+    const uint32_t c = w + 2 < nwords ? __byte_perm(__ldg(words + w + 2), 0, 0x0123) : 0u;
+    return ((uint64_t)__funnelshift_l(b, a, sh) << 32) | __funnelshift_l(c, b, sh);
+}
+
+// xdrfile's receiveints layout: of the nbits (1..64, here the top bits of X) the first `full` whole bytes are the
+// value's low bytes, least significant first, the last `part` (1..8) bits its top
+__device__ __forceinline__ uint64_t packed_value(uint64_t X, int nbits, int full, int part) {
+    const uint64_t x = X >> (64 - nbits);
+    const uint64_t top = x >> part;
+    const uint32_t lsb = (uint32_t)x & ((1u << part) - 1u);
+    const uint64_t rev = ((uint64_t)__byte_perm((uint32_t)top, 0, 0x0123) << 32) | __byte_perm((uint32_t)(top >> 32), 0, 0x0123);
+    const uint64_t low = full ? rev >> (64 - 8 * full) : 0ull;
+    return low | ((uint64_t)lsb << (8 * full));
+}
+
+__global__ void __launch_bounds__(kGroupThreads) xtc_groups_kernel(const WalkParams wp) {
+    const DecodeParams& prm = wp.d;
+    const int64_t f = blockIdx.y;
+    const FrameRec* rp = wp.rec + f;
+    const int ngroups = rp->ngroups;
+    const int g0 = (int)blockIdx.x * kGroupsPerCta;
+    if (g0 >= ngroups) return;
+    const int g1 = min(ngroups, g0 + kGroupsPerCta);
+    const int natoms = prm.natoms;
+    const int32_t minint[3] = {rp->minint[0], rp->minint[1], rp->minint[2]};
+    const uint32_t sizeint[3] = {rp->sizeint[0], rp->sizeint[1], rp->sizeint[2]};
+    const int bitsint[3] = {rp->bitsint[0], rp->bitsint[1], rp->bitsint[2]};
+    const int bitsize = rp->bitsize;
+    const bool big_fast = rp->big_fast != 0;
+    const uint64_t rcp1 = rp->rcp1, rcp2 = rp->rcp2;
+    const float inv = rp->inv;
+    const uint8_t* sbase = prm.data + rp->stream_off;
+    const uint8_t* send = sbase + rp->stream_bytes;
+    const uint32_t* words = reinterpret_cast<const uint32_t*>(sbase);
+    const uint32_t nwords = rp->stream_bytes >> 2;
+    const int bigbits = bitsize ? bitsize : bitsint[0] + bitsint[1] + bitsint[2];
+    const int bfull = bitsize ? (bitsize - 1) >> 3 : 0, bpart = bitsize - 8 * bfull;
+    float* out = prm.xyz + (size_t)f * prm.nsel * 3;
+    const int32_t* slot = prm.slot;
+    const uint2* desc = wp.desc + (size_t)f * natoms;
+    auto emit = [&](int atom, int32_t c0, int32_t c1, int32_t c2) {
+        const int s = slot ? slot[atom] : atom;
+        if (s >= 0 && s < prm.nsel) {
+            float* o = out + 3 * (size_t)s;
+            o[0] = (float)c0 * inv; o[1] = (float)c1 * inv; o[2] = (float)c2 * inv;
+        }
+    };
+    for (int g = g0 + (int)threadIdx.x; g < g1; g += kGroupThreads) {
+        const uint2 dsc = desc[g];
+        const uint32_t pos = dsc.x;
+        const int my_first = (int)(dsc.y & 0x1fffffu), my_ns = (int)((dsc.y >> 21) & 15u), my_sidx = (int)(dsc.y >> 25);
+        int32_t cur[3];
+        if (big_fast) {
+            // value = (c0 * s1 + c1) * s2 + c2
+            const uint64_t v = packed_value(peek64(words, nwords, pos), bitsize, bfull, bpart);
+            uint32_t r2, r1;
+            const uint64_t qq = divmod64(v, sizeint[2], rcp2, r2);
+            const uint64_t q2 = divmod64(qq, sizeint[1], rcp1, r1);
+            cur[2] = (int32_t)r2; cur[1] = (int32_t)r1; cur[0] = (int32_t)q2;
+        } else {
+            BitStream bs;
+            bs.init_at(sbase, send, (int64_t)pos);
+            if (bitsize == 0) {
+                for (int d = 0; d < 3; d++) cur[d] = (int32_t)bs.get(bitsint[d]);
+            } else {
+                const Triple t = unpack3_wide(bs, bitsize, sizeint[1], sizeint[2]);
+                for (int d = 0; d < 3; d++) cur[d] = t.c[d];
+            }
+        }
+        for (int d = 0; d < 3; d++) cur[d] += minint[d];
+        if (my_ns == 0) {
+            emit(my_first, cur[0], cur[1], cur[2]);
+            continue;
+        }
+        // the flag behind the full-size code, five run bits if it is set, then the small codes
+        uint32_t sp = pos + (uint32_t)bigbits;
+        {
+            const uint32_t w = sp >> 5;
+            const uint32_t fw = w < nwords ? __byte_perm(__ldg(words + w), 0, 0x0123) : 0u;
+            sp += ((fw >> (31 - (sp & 31))) & 1u) ? 6u : 1u;
+        }
+        const uint32_t sizesmall = (uint32_t)c_magic[my_sidx];
+        const int smallnum = (int)(sizesmall >> 1);
+        int32_t prev[3] = {cur[0], cur[1], cur[2]};
+        int a = my_first + 1;
+        if (my_sidx <= 32) {
+            const uint32_t rcpsmall = c_rcp_magic[my_sidx];
+            const int sfull = (my_sidx - 1) >> 3, spart = my_sidx - 8 * sfull;
+            for (int k = 0; k < my_ns; k++, sp += (uint32_t)my_sidx) {
+                const uint32_t v = (uint32_t)packed_value(peek64(words, nwords, sp), my_sidx, sfull, spart);
+                uint32_t r2, r1;
+                const uint32_t qq = divmod32(v, sizesmall, rcpsmall, r2);
+                const uint32_t q2 = divmod32(qq, sizesmall, rcpsmall, r1);
+                cur[0] = (int32_t)q2 + prev[0] - smallnum;
+                cur[1] = (int32_t)r1 + prev[1] - smallnum;
+                cur[2] = (int32_t)r2 + prev[2] - smallnum;
+                if (k == 0) {
+                    // the first two atoms of a run are stored in swapped order
+                    emit(my_first, cur[0], cur[1], cur[2]);
+                    emit(a++, prev[0], prev[1], prev[2]);
+                } else {
+                    emit(a++, cur[0], cur[1], cur[2]);
+                }
+                for (int d = 0; d < 3; d++) prev[d] = cur[d];
+            }
+        } else {
+            BitStream bs;
+            bs.init_at(sbase, send, (int64_t)sp);
+            for (int k = 0; k < my_ns; k++) {
+                const Triple t = unpack3_wide(bs, my_sidx, sizesmall, sizesmall);
+                for (int d = 0; d < 3; d++) cur[d] = t.c[d] + prev[d] - smallnum;
+                if (k == 0) {
+                    emit(my_first, cur[0], cur[1], cur[2]);
+                    emit(a++, prev[0], prev[1], prev[2]);
+                } else {
+                    emit(a++, cur[0], cur[1], cur[2]);
+                }
+                for (int d = 0; d < 3; d++) prev[d] = cur[d];
+            }
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" int conan_xtc_decode_device(const uint8_t* d_data, int64_t nbytes, const int64_t* d_offsets,
@@ -348,5 +685,59 @@ extern "C" int conan_xtc_decode_device(const uint8_t* d_data, int64_t nbytes, co
     const unsigned blocks = (unsigned)((nframes + per_block - 1) / per_block);
     xtc_decode_kernel<<<blocks, kDecodeThreads, 0, static_cast<cudaStream_t>(stream)>>>(prm);
     CONAN_CUDA_TRY(cudaGetLastError());
+    return CONAN_OK;
+}
+
+extern "C" size_t conan_xtc_decode_workspace_bytes(int64_t nframes, int32_t natoms) {
+    if (nframes <= 0 || natoms <= 0) return 0;
+    return (size_t)nframes * (sizeof(FrameRec) + (size_t)natoms * sizeof(uint2));
+}
+
+extern "C" int conan_xtc_decode_device_ws(const uint8_t* d_data, int64_t nbytes, const int64_t* d_offsets,
+                                          int64_t nframes, int32_t natoms, const int32_t* d_slot, int32_t nsel,
+                                          float* d_xyz, int32_t* d_status, void* d_work, size_t work_bytes,
+                                          void* stream) {
+    if (!d_data || !d_offsets || !d_xyz || !d_status || nbytes < 0 || nframes < 0 || natoms < 0 || nsel < 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_decode_device_ws: bad arguments");
+    if ((reinterpret_cast<uintptr_t>(d_data) & 3) != 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_decode_device_ws: d_data must be 4-byte aligned");
+    if (!d_slot && nsel != natoms)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_decode_device_ws: without a slot map nsel must equal natoms");
+    if (nframes == 0) return CONAN_OK;
+    if (natoms > kMaxWsAtoms)     // the descriptors hold 21 bits of atom index: larger systems take the one-pass kernel
+        return conan_xtc_decode_device(d_data, nbytes, d_offsets, nframes, natoms, d_slot, nsel, d_xyz, d_status, stream);
+    const size_t per_frame = sizeof(FrameRec) + (size_t)natoms * sizeof(uint2);
+    if (!d_work || (reinterpret_cast<uintptr_t>(d_work) & 15) != 0 || work_bytes < per_frame)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_decode_device_ws: the workspace must be 16-byte aligned and hold at "
+                                          "least one frame (%zu bytes)", per_frame);
+    // as many frames per pass as the workspace holds (records first, descriptors behind them)
+    const int64_t chunk = (int64_t)std::min<size_t>((size_t)nframes, std::min<size_t>(work_bytes / per_frame, 65535));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    {
+        // the walk's windows need more than the default 48 KB of shared memory: once per device
+        static std::atomic<uint64_t> configured{0};
+        int dev = 0;
+        CONAN_CUDA_TRY(cudaGetDevice(&dev));
+        const uint64_t bit = 1ull << (dev & 63);
+        if (!(configured.load(std::memory_order_acquire) & bit)) {
+            CONAN_CUDA_TRY(cudaFuncSetAttribute(xtc_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWalkSmem));
+            configured.fetch_or(bit, std::memory_order_release);
+        }
+    }
+    for (int64_t f0 = 0; f0 < nframes; f0 += chunk) {
+        const int64_t n = std::min(chunk, nframes - f0);
+        WalkParams wp;
+        wp.d = DecodeParams{d_data, nbytes, d_offsets + f0, n, natoms, d_slot, nsel, d_xyz + (size_t)f0 * nsel * 3,
+                            d_status + f0};
+        wp.rec = static_cast<FrameRec*>(d_work);
+        wp.desc = reinterpret_cast<uint2*>(static_cast<unsigned char*>(d_work) + (size_t)chunk * sizeof(FrameRec));
+        xtc_walk_kernel<<<(unsigned)((n + 32 * kWalkWarps - 1) / (32 * kWalkWarps)), 32 * kWalkWarps, kWalkSmem, st>>>(wp);
+        CONAN_CUDA_TRY(cudaGetLastError());
+        if (natoms > 9) {
+            const dim3 grid((unsigned)((natoms + kGroupsPerCta - 1) / kGroupsPerCta), (unsigned)n);
+            xtc_groups_kernel<<<grid, kGroupThreads, 0, st>>>(wp);
+            CONAN_CUDA_TRY(cudaGetLastError());
+        }
+    }
     return CONAN_OK;
 }

@@ -397,7 +397,7 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     host_free = [None, None]      # event after the H2D copy that read each pinned buffer
     dev_free = [None, None]       # event after the kernel that read each device staging buffer
     if is_xtc:
-        # The compressed frames go to the GPU as they are on disk and are decoded there (conan_xtc_decode_device).
+        # The compressed frames go to the GPU as they are on disk and are decoded there (conan_xtc_decode_device_ws).
         # Two pinned staging buffers and a copy stream: the bytes of batch b+1 travel while batch b is decoded and
         # its distances are computed; nothing waits on the host between batches.
         lib = _lib.load()
@@ -415,6 +415,9 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
         slot = np.full(x.natoms, -1, np.int32)
         slot[np.asarray(sel, dtype=np.int64)] = np.arange(len(sel), dtype=np.int32)
         d_slot = torch.from_numpy(slot).to(dev)
+        # scratch of the two-pass decoder, at most 1 GiB (with less than a batch's worth the frames go in rounds)
+        d_dec_work = torch.empty(max(96 + 8 * x.natoms, min(int(lib.conan_xtc_decode_workspace_bytes(batch, x.natoms)), 1 << 30)),
+                                 dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             for n, (b0, ids, lo_b, hi_b) in enumerate(spans):
                 k = n % 2
@@ -432,9 +435,10 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
                     copied.record(copy_stream)
                 host_free[k] = copied
                 main_stream.wait_event(copied)
-                _lib.check(lib.conan_xtc_decode_device(d_stage[k].data_ptr(), nbytes, d_off[k].data_ptr(), len(ids), x.natoms,
-                                                       d_slot.data_ptr(), len(sel), d_coords.data_ptr(),
-                                                       d_status[b0:b0 + len(ids)].data_ptr(), main_stream.cuda_stream))
+                _lib.check(lib.conan_xtc_decode_device_ws(d_stage[k].data_ptr(), nbytes, d_off[k].data_ptr(), len(ids), x.natoms,
+                                                          d_slot.data_ptr(), len(sel), d_coords.data_ptr(),
+                                                          d_status[b0:b0 + len(ids)].data_ptr(), d_dec_work.data_ptr(),
+                                                          d_dec_work.numel(), main_stream.cuda_stream))
                 decoded = torch.cuda.Event()
                 decoded.record(main_stream)
                 dev_free[k] = decoded

@@ -69,10 +69,13 @@ class XtcFile:
                                             out.ctypes.data, nthreads))
         return out
 
-    def decode_device(self, frame_ids=None, atom_sel=None, device="cuda", out=None, stream=None):
-        """Decode frames on the GPU (conan_xtc_decode_device): the compressed bytes of the frame range are
-        copied to the device and each frame is decoded by one thread.  Returns a float32 device tensor
-        [n, nsel, 3]; raises ConanError if any frame is malformed (this call synchronises to check)."""
+    def decode_device(self, frame_ids=None, atom_sel=None, device="cuda", out=None, stream=None, one_pass=False,
+                      work_bytes=None):
+        """Decode frames on the GPU: the compressed bytes of the frame range are copied to the device and decoded
+        there, in two passes with scratch memory (conan_xtc_decode_device_ws; work_bytes limits the scratch, the
+        frames are then taken in rounds) or, one_pass=True, by one warp per frame (conan_xtc_decode_device).
+        Returns a float32 device tensor [n, nsel, 3]; raises ConanError if any frame is malformed (this call
+        synchronises to check)."""
         import torch
         lib = _lib.load()
         dev = torch.device(device)
@@ -103,9 +106,19 @@ class XtcFile:
         d_status = torch.full((frame_ids.size,), -1, dtype=torch.int32, device=dev)
         st = stream if stream is not None else torch.cuda.current_stream(dev).cuda_stream
         with torch.cuda.device(dev):
-            _lib.check(lib.conan_xtc_decode_device(d_data.data_ptr(), b1 - b0, d_off.data_ptr(), frame_ids.size,
-                                                   self.natoms, None if d_slot is None else d_slot.data_ptr(), nout,
-                                                   out.data_ptr(), d_status.data_ptr(), st))
+            if one_pass:
+                _lib.check(lib.conan_xtc_decode_device(d_data.data_ptr(), b1 - b0, d_off.data_ptr(), frame_ids.size,
+                                                       self.natoms, None if d_slot is None else d_slot.data_ptr(), nout,
+                                                       out.data_ptr(), d_status.data_ptr(), st))
+            else:
+                need = int(lib.conan_xtc_decode_workspace_bytes(frame_ids.size, self.natoms))
+                if work_bytes is not None:
+                    need = min(need, int(work_bytes))
+                d_work = torch.empty(max(need, 16), dtype=torch.uint8, device=dev)
+                _lib.check(lib.conan_xtc_decode_device_ws(d_data.data_ptr(), b1 - b0, d_off.data_ptr(), frame_ids.size,
+                                                          self.natoms, None if d_slot is None else d_slot.data_ptr(), nout,
+                                                          out.data_ptr(), d_status.data_ptr(), d_work.data_ptr(),
+                                                          d_work.numel(), st))
         bad = torch.nonzero(d_status).flatten()
         if bad.numel():
             k = int(bad[0].item())

@@ -89,6 +89,21 @@ int conan_xtc_decode_device(const uint8_t* d_data, int64_t nbytes, const int64_t
                             int32_t natoms, const int32_t* d_slot, int32_t nsel, float* d_xyz,
                             int32_t* d_status, void* stream);
 
+/* The same decode in two passes, for callers that can lend scratch memory; about three times faster on
+ * streams whose run flags change often.  Pass 1 walks the run flags of every frame with one thread per
+ * frame (the walk is a short serial chain per group of atoms: 32 frames share an issue slot instead of
+ * one frame holding a warp) and writes an 8-byte descriptor per group; pass 2 decodes the groups with
+ * one thread each.  Same arguments, results and status codes as conan_xtc_decode_device.
+ * d_work / work_bytes  16-byte aligned scratch; conan_xtc_decode_workspace_bytes(nframes, natoms)
+ *            = nframes * (96 + 8 * natoms) holds all frames at once; with less the frames are taken in
+ *            as many rounds as needed (each round costs the latency of one frame's walk, ~0.3 ms per
+ *            8000 atoms), with less than one frame's worth the call is refused.
+ * Systems of more than 2^21 atoms take the one-pass kernel (the descriptors keep 21 bits of atom index). */
+size_t conan_xtc_decode_workspace_bytes(int64_t nframes, int32_t natoms);
+int conan_xtc_decode_device_ws(const uint8_t* d_data, int64_t nbytes, const int64_t* d_offsets, int64_t nframes,
+                               int32_t natoms, const int32_t* d_slot, int32_t nsel, float* d_xyz,
+                               int32_t* d_status, void* d_work, size_t work_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------ */
 /* Stage 1: per-frame residue-residue minimum-distance matrix, quantised to xpm levels.  */
 /* Replaces `gmx mdmat -frames` as invoked by conan.py:1437-1453 (:1783-1784) and the    */

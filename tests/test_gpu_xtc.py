@@ -1,5 +1,8 @@
-"""conan_xtc_decode_device (one thread per frame on the GPU) against the host decoder and the oracle:
-bit-identical coordinates on the reference's own trajectories and on synthetic compressed ones."""
+"""The GPU decoders -- conan_xtc_decode_device_ws (two passes: one thread per frame walks the run flags, one
+thread per group of atoms decodes) and conan_xtc_decode_device (one warp per frame) -- against the host decoder
+and the oracle: bit-identical coordinates on the reference's own trajectories and on synthetic compressed ones.
+Every test runs with the two-pass decoder holding all frames at once, with scratch for three frames only (the
+frames are then taken in rounds) and with the one-pass decoder."""
 import os
 
 import numpy as np
@@ -16,6 +19,21 @@ def torch_cuda():
     if not torch.cuda.is_available():
         pytest.skip("needs a GPU")
     return torch
+
+
+@pytest.fixture(autouse=True, params=["two_pass", "two_pass_rounds", "one_pass"])
+def decoder(request, monkeypatch):
+    from conan_b200.xtc import XtcFile
+    plain = XtcFile.decode_device
+
+    def decode_device(self, *a, **k):
+        if request.param == "one_pass":
+            k["one_pass"] = True
+        elif request.param == "two_pass_rounds":
+            k["work_bytes"] = 3 * (96 + 8 * self.natoms)
+        return plain(self, *a, **k)
+    monkeypatch.setattr(XtcFile, "decode_device", decode_device)
+    return request.param
 
 
 @pytest.mark.parametrize("name", ["sample.xtc", "ubi_12.xtc"])
