@@ -659,9 +659,12 @@ def run_stage3(args, dev):
                                              out=dist_out), reps=2)
     pk, kind = peaks()
     tf32_peak = pk["bf16_tflops"]             # the split parts are binary16: the MMAs run on the f16 / bf16 path
-    ntile = lambda n: (n + 127) // 128
-    mma_cov = 3 * 2.0 * (ntile(len(seen)) * (ntile(len(seen)) + 1) / 2) * 128 * 128 * ((nf + 63) // 64 * 64)
-    mma_ff = 3 * 2.0 * (ntile(nff) * (ntile(nff) + 1) / 2) * 128 * 128 * ((len(seen) + 63) // 64 * 64)
+    # MMA flops issued: upper-triangle tiles (diagonal ones whole) of the kernel in use: 256 x 256 per CTA pair,
+    # or 128 x 128 with CONAN_GEMM_CFG=0
+    tile = 128 if os.environ.get("CONAN_GEMM_CFG", "1") == "0" else 256
+    ntile = lambda n: (n + tile - 1) // tile
+    mma_cov = 3 * 2.0 * (ntile(len(seen)) * (ntile(len(seen)) + 1) / 2) * tile * tile * ((nf + 63) // 64 * 64)
+    mma_ff = 3 * 2.0 * (ntile(nff) * (ntile(nff) + 1) / 2) * tile * tile * ((len(seen) + 63) // 64 * 64)
     return {
         "workload": "C3: %d residues x %d frames, %d of %d pairs ever in contact" % (nres, nf, len(seen), P),
         "pearson": {"ms": ms_pearson, "observables": 3, "bound": "hbm", "achieved": 2.0 * P * nf / ms_pearson / 1e6, "unit": "GB/s",

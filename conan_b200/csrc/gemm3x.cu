@@ -26,6 +26,7 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.h"
 
@@ -264,6 +265,206 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// CTA pairs.  The single-CTA kernel above is bound by the bytes it stages per MMA: 64 KB of operand tiles per
+// k-block and SM.  Here two CTAs on neighbouring SMs (a cluster of two) compute one 256 x 256 tile with
+// tcgen05.mma.cta_group::2: each CTA stages its own 128 rows of A and its own 128 of the tile's 256 B rows
+// -- the same 64 KB per k-block -- and the pair's MMAs (M = 256, N = 256, issued by the even CTA, reading both
+// CTAs' shared memory) do twice the work on them.  Each CTA's TMEM holds its 128 rows x 256 columns, twice
+// (all 512 columns), for the same chunked hand-over: 128 k-values per accumulator, drained by sixteen
+// epilogue warps (a quarter of the lanes x a quarter of the columns each) into round-to-nearest sums.
+// All tensor maps cover this GPU's memory only, and no load is multicast: the pair shares operands through
+// the MMA's own reads of the partner's shared memory.
+// ------------------------------------------------------------------------------------------
+constexpr int kPairThreads = 576;                    // TMA warp, MMA warp, sixteen epilogue warps
+constexpr int kPairBN = 256;                         // columns of the pair's tile (and of each CTA's accumulator)
+constexpr int kPairTmemCols = 512;
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;       // a shared::cluster address with this bit cleared names the even CTA of the pair
+// kind::f16, D = F32, A / B binary16 K-major, M = 256 (the pair), N = 256
+constexpr uint32_t kInstrDescPair = (1u << 4) | ((uint32_t)(kPairBN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    // the bytes are counted on the even CTA's barrier, whichever CTA of the pair issues the load
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(kInstrDescPair), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    // arrives on the barrier at this offset in both CTAs once the pair's MMAs issued so far have retired
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_even_cta(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
+gemm3x_pair_kernel(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__ CUtensorMap mapAl,
+                   const __grid_constant__ CUtensorMap mapBh, const __grid_constant__ CUtensorMap mapBl,
+                   const GemmParams prm) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], tmem_full_bar[2], tmem_empty_bar[2];
+    __shared__ uint32_t tmem_base_slot;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();           // 0: the even CTA, which issues the pair's MMAs
+    // tiles of 256 x 256, walked in bands of kBand / 2 tile rows (see the single-CTA kernel)
+    constexpr int kBandP = kBand / 2;
+    const int ntm = (prm.M + 255) / 256, ntn = (prm.N + kPairBN - 1) / kPairBN;
+    const int pair = (int)(blockIdx.x >> 1);
+    const int band = pair / (kBandP * ntn);
+    const int rows_in_band = min(kBandP, ntm - band * kBandP);
+    const int within = pair - band * kBandP * ntn;
+    const int tn = within / rows_in_band;
+    const int tm = band * kBandP + within % rows_in_band;
+    if (prm.symmetric && tn < tm) return;              // both CTAs of the pair leave together
+    const int m0 = tm * 256 + (int)rank * kBM;          // this CTA's rows of the tile
+    const int n0 = tn * kPairBN;
+    const int nkb = prm.K / kBK;
+    const int nchunks = (nkb + kChunkKb - 1) / kChunkKb;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        // an accumulator is free again when the sixteen epilogue warps of both CTAs have drained it
+        for (int b = 0; b < 2; b++) { mbar_init(&tmem_full_bar[b], 1); mbar_init(&tmem_empty_bar[b], 32); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)),
+                     "n"(kPairTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    cluster_sync_all();        // barriers of both CTAs initialised, TMEM of both allocated
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ---- TMA producer (one thread in each CTA) ----
+        if (lane == 0) {
+            for (int kb = 0; kb < nkb; kb++) {
+                const int s = kb % kStages;
+                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                mbar_wait(&empty_bar[s], ph ^ 1u, 0);
+                unsigned char* st = smem + (size_t)s * kStageBytes;
+                if (rank == 0) mbar_expect_tx(&full_bar[s], 2 * kStageBytes);     // both CTAs' bytes
+                tma_load_2d_pair(st, &mapAh, &full_bar[s], kb * kBK, m0);
+                tma_load_2d_pair(st + kOperandBytes, &mapAl, &full_bar[s], kb * kBK, m0);
+                tma_load_2d_pair(st + 2 * kOperandBytes, &mapBh, &full_bar[s], kb * kBK, n0 + (int)rank * kBM);
+                tma_load_2d_pair(st + 3 * kOperandBytes, &mapBl, &full_bar[s], kb * kBK, n0 + (int)rank * kBM);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ---- MMA issuer: one thread of the even CTA ----
+        if (lane == 0 && rank == 0) {
+            for (int kb = 0; kb < nkb; kb++) {
+                const int s = kb % kStages;
+                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                const int chunk = kb / kChunkKb, buf = chunk & 1;
+                const bool chunk_start = (kb % kChunkKb) == 0;
+                if (chunk_start) {
+                    mbar_wait(&tmem_empty_bar[buf], ((uint32_t)(chunk >> 1) & 1u) ^ 1u, 3);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
+                mbar_wait(&full_bar[s], ph, 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t acc = tmem_base + (uint32_t)(buf * kPairBN);
+                const uint32_t base = smem_u32(smem + (size_t)s * kStageBytes);
+                const uint64_t dAh = make_smem_desc(base), dAl = make_smem_desc(base + kOperandBytes);
+                const uint64_t dBh = make_smem_desc(base + 2 * kOperandBytes), dBl = make_smem_desc(base + 3 * kOperandBytes);
+#pragma unroll
+                for (int k = 0; k < kBK / kUmmaK; k++) {
+                    const uint64_t adv = (uint64_t)((k * kUmmaK * 2) >> 4);
+                    umma_f16_pair(acc, dAh + adv, dBh + adv, !(chunk_start && k == 0));
+                    umma_f16_pair(acc, dAh + adv, dBl + adv, 1);
+                    umma_f16_pair(acc, dAl + adv, dBh + adv, 1);
+                }
+                umma_commit_pair(&empty_bar[s]);
+                if ((kb % kChunkKb) == kChunkKb - 1 || kb == nkb - 1) umma_commit_pair(&tmem_full_bar[buf]);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---- epilogue: sixteen warps; warp w owns TMEM lanes 32 (w & 3) .. and 64 of the 256 columns ----
+        const int q = warp & 3, cq = (warp - 2) >> 2;
+        constexpr int kCols = kPairBN / 4;
+        float racc[kCols];
+#pragma unroll
+        for (int j = 0; j < kCols; j++) racc[j] = 0.f;
+        for (int chunk = 0; chunk < nchunks; chunk++) {
+            const int buf = chunk & 1;
+            mbar_wait(&tmem_full_bar[buf], (uint32_t)(chunk >> 1) & 1u, 2);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int c = 0; c < kCols / 32; c++) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * kPairBN + cq * kCols + c * 32), v);
+#pragma unroll
+                for (int j = 0; j < 32; j++) racc[c * 32 + j] += __uint_as_float(v[j]);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive_even_cta(&tmem_empty_bar[buf]);
+        }
+        const int m = m0 + q * 32 + lane;
+        const float rn = (prm.epilogue == 1 && m < prm.M) ? (float)prm.row_norm2[m] : 0.f;
+#pragma unroll
+        for (int c = 0; c < kCols / 32; c++) {
+            const int nb = n0 + cq * kCols + c * 32;
+            float o[32];
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                const float acc = racc[c * 32 + j];
+                if (prm.epilogue == 1) {
+                    const float cn = (nb + j < prm.N) ? (float)prm.col_norm2[nb + j] : 0.f;
+                    o[j] = prm.alpha * sqrtf(fmaxf(rn + cn - 2.f * acc, 0.f));
+                } else {
+                    o[j] = prm.alpha * acc;
+                }
+            }
+            if (m < prm.M) {
+                float* dst = prm.C + (size_t)m * prm.ldc + nb;
+                if (nb + 32 <= prm.N && (prm.ldc & 3) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+                } else {
+                    for (int j = 0; j < 32; j++) if (nb + j < prm.N) dst[j] = o[j];
+                }
+                if (prm.symmetric && tm != tn) {
+                    for (int j = 0; j < 32; j++)
+                        if (nb + j < prm.N) prm.C[(size_t)(nb + j) * prm.ldc + m] = o[j];
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    // nobody leaves while the partner may still signal its barriers or read its shared memory
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kPairTmemCols) : "memory");
+    }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
@@ -325,10 +526,21 @@ extern "C" int conan_gemm_3xtf32(const uint16_t* d_a_hi, const uint16_t* d_a_lo,
     prm.C = d_c; prm.ldc = ldc; prm.epilogue = epilogue; prm.alpha = alpha;
     prm.row_norm2 = d_row_norm2; prm.col_norm2 = d_col_norm2; prm.symmetric = symmetric ? 1 : 0;
     const size_t smem = (size_t)kStages * kStageBytes + 1024;
-    CONAN_CUDA_TRY(cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int tmn = (M + kBM - 1) / kBM, tnn = (N + kBN - 1) / kBN;
-    dim3 grid((unsigned)(tmn * tnn), 1);
-    gemm3x_kernel<<<grid, kThreads, smem, stream>>>(mAh, mAl, mBh, mBl, prm);
+    // CTA pairs (256 x 256 tiles) unless the problem is a single tile wide or CONAN_GEMM_CFG=0 asks for the
+    // single-CTA kernel (128 x 128 tiles)
+    const char* cfg = getenv("CONAN_GEMM_CFG");
+    const bool pairs = cfg ? atoi(cfg) != 0 : (M > kBM || N > kBN);
+    if (pairs) {
+        CONAN_CUDA_TRY(cudaFuncSetAttribute(gemm3x_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int tmn = (M + 255) / 256, tnn = (N + kPairBN - 1) / kPairBN;
+        dim3 grid((unsigned)(2 * tmn * tnn), 1);
+        gemm3x_pair_kernel<<<grid, kPairThreads, smem, stream>>>(mAh, mAl, mBh, mBl, prm);
+    } else {
+        CONAN_CUDA_TRY(cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int tmn = (M + kBM - 1) / kBM, tnn = (N + kBN - 1) / kBN;
+        dim3 grid((unsigned)(tmn * tnn), 1);
+        gemm3x_kernel<<<grid, kThreads, smem, stream>>>(mAh, mAl, mBh, mBl, prm);
+    }
     CONAN_CUDA_TRY(cudaGetLastError());
     return CONAN_OK;
 }

@@ -315,7 +315,11 @@ int conan_build_operand(const uint16_t* d_levels, int64_t levels_stride, int64_t
  *                                               operand's power-of-two scale)
  * epilogue 1: alpha * sqrt(max(0, row_norm2[m] + col_norm2[n] - 2 acc))   (frame-frame distance,
  *                                               conan.py:2063; alpha = 1/s)
- * symmetric != 0 (needs A == B): only the upper triangle of 128 x 128 tiles is computed, both halves written. */
+ * symmetric != 0 (needs A == B): only the upper triangle of tiles is computed, both halves written.
+ * Two kernels: CTA pairs on 256 x 256 tiles (tcgen05.mma.cta_group::2; each CTA stages its own half of both
+ * operands, so the pair does twice the MMA work per staged byte) whenever the problem is wider than one
+ * 128 x 128 tile, else one CTA per 128 x 128 tile; the environment variable CONAN_GEMM_CFG (0 / 1) forces the
+ * single-CTA / the pair kernel.  M, N and K are 32-bit; K (padded to 64) must stay below 2^31. */
 int conan_gemm_3xtf32(const uint16_t* d_a_hi, const uint16_t* d_a_lo, int32_t M, const uint16_t* d_b_hi,
                       const uint16_t* d_b_lo, int32_t N, int64_t K, int64_t ld, int32_t epilogue, float alpha,
                       const double* d_row_norm2, const double* d_col_norm2, int32_t symmetric, float* d_c,

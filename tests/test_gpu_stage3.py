@@ -65,8 +65,16 @@ def test_linregress_matches_scipy(lib, nf, P, nlevels, trunc):
     assert _frob(np.where(varying, res["r"][0], 0.0), want) < 1e-6
 
 
+@pytest.fixture(params=["pairs", "single"])
+def gemm_kernel(request, monkeypatch):
+    """conan_gemm_3xtf32 under both of its kernels: CTA pairs on 256 x 256 tiles (the default for anything wider
+    than one 128 x 128 tile) and the single-CTA kernel."""
+    monkeypatch.setenv("CONAN_GEMM_CFG", "1" if request.param == "pairs" else "0")
+    return request.param
+
+
 @pytest.mark.parametrize("nf,P,nlevels", [(500, 300, 1001), (130, 77, 101), (2000, 513, 1001)])
-def test_covariance_matches_numpy(lib, nf, P, nlevels):
+def test_covariance_matches_numpy(lib, gemm_kernel, nf, P, nlevels):
     from conan_b200 import stage3
     from conan_b200.levels import legend_values
     rng = np.random.default_rng(P)
@@ -85,7 +93,7 @@ def test_covariance_matches_numpy(lib, nf, P, nlevels):
 
 
 @pytest.mark.parametrize("nf,P,nlevels", [(400, 350, 1001), (129, 50, 101), (1500, 2000, 1001)])
-def test_frame_distances_match_pdist(lib, nf, P, nlevels):
+def test_frame_distances_match_pdist(lib, gemm_kernel, nf, P, nlevels):
     from scipy.spatial.distance import pdist, squareform
     from conan_b200 import stage3
     from conan_b200.levels import legend_values
@@ -105,12 +113,13 @@ def test_frame_distances_match_pdist(lib, nf, P, nlevels):
     assert np.abs(np.diag(got)).max() < 2e-3      # the diagonal is sqrt of rounding noise, never read by the callers
 
 
-def test_gemm_general_rectangular(lib):
-    """A != B, sizes that are not multiples of the tile, plain scaling epilogue."""
+@pytest.mark.parametrize("M,N,K", [(200, 333, 70), (700, 1100, 1000), (64, 900, 130), (257, 100, 64)])
+def test_gemm_general_rectangular(lib, gemm_kernel, M, N, K):
+    """A != B, sizes that are not multiples of the tile (several tiles either way, one side narrower than a
+    tile), plain scaling epilogue."""
     import torch
     from conan_b200 import stage3
     rng = np.random.default_rng(0)
-    M, N, K = 200, 333, 70
     a, b = rng.normal(size=(M, K)), rng.normal(size=(N, K))
 
     def split(x, scale=64.0):

@@ -14,7 +14,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-fil
 for k in mdmat_tile_kernel pair_stats_kernel prep_slots_kernel; do
   ncu --set full --clock-control none --import-source on -k regex:$k -c 1 -o $out/${tag}_$k $small --no-stage3 > $out/${tag}_$k.log 2>&1
 done
-for k in gemm3x_kernel pearson_sums_kernel sym_block_matvec_kernel operand_pairs_kernel; do
+for k in gemm3x_pair_kernel pearson_sums_kernel sym_block_matvec_kernel operand_pairs_kernel; do
   ncu --set full --clock-control none --import-source on -k regex:$k -c 1 -o $out/${tag}_$k $small > $out/${tag}_$k.log 2>&1
 done
 ncu --set full --clock-control none --import-source on -k regex:xtc_decode_kernel -c 1 -o $out/${tag}_xtc_decode_kernel python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-configs --no-stage3 > $out/${tag}_xtc.log 2>&1
