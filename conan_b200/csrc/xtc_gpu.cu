@@ -345,6 +345,7 @@ __global__ void __launch_bounds__(kDecodeThreads, 8) xtc_decode_kernel(const Dec
 constexpr int kMaxWsAtoms = 1 << 21;      // `first` has 21 bits in a descriptor
 constexpr int kGroupThreads = 128;
 constexpr int kGroupsPerCta = 512;
+constexpr int kRunQueue = 64;           // parked runs per warp (at most 31 waiting + 32 new)
 
 struct __align__(16) FrameRec {
     int64_t stream_off;      // byte offset of the code stream inside d_data
@@ -592,80 +593,120 @@ __global__ void __launch_bounds__(kGroupThreads) xtc_groups_kernel(const WalkPar
             o[0] = (float)c0 * inv; o[1] = (float)c1 * inv; o[2] = (float)c2 * inv;
         }
     };
-    for (int g = g0 + (int)threadIdx.x; g < g1; g += kGroupThreads) {
-        const uint2 dsc = desc[g];
-        const uint32_t pos = dsc.x;
-        const int my_first = (int)(dsc.y & 0x1fffffu), my_ns = (int)((dsc.y >> 21) & 15u), my_sidx = (int)(dsc.y >> 25);
-        int32_t cur[3];
-        if (big_fast) {
-            // value = (c0 * s1 + c1) * s2 + c2
-            const uint64_t v = packed_value(peek64(words, nwords, pos), bitsize, bfull, bpart);
-            uint32_t r2, r1;
-            const uint64_t qq = divmod64(v, sizeint[2], rcp2, r2);
-            const uint64_t q2 = divmod64(qq, sizeint[1], rcp1, r1);
-            cur[2] = (int32_t)r2; cur[1] = (int32_t)r1; cur[0] = (int32_t)q2;
-        } else {
-            BitStream bs;
-            bs.init_at(sbase, send, (int64_t)pos);
-            if (bitsize == 0) {
-                for (int d = 0; d < 3; d++) cur[d] = (int32_t)bs.get(bitsint[d]);
+    // Groups with small codes behind the full-size one are rare and long (a dependent chain of up to ten
+    // codes), so they are not decoded where they are met: the lane parks them in a queue of its warp, and
+    // whenever 32 are waiting (and once more at the end) the warp decodes one run per lane.
+    __shared__ uint32_t q_pos[kGroupThreads / 32][kRunQueue], q_meta[kGroupThreads / 32][kRunQueue];
+    __shared__ int32_t q_prev[kGroupThreads / 32][3][kRunQueue];
+    const int warp = (int)threadIdx.x >> 5, lane = (int)threadIdx.x & 31;
+    uint32_t* qp = q_pos[warp];
+    uint32_t* qm = q_meta[warp];
+    int queued = 0;                 // warp-uniform
+
+    auto decode_runs = [&](int from, int n) {         // n (<= 32) entries of the queue starting at `from`, one per lane
+        if (lane < n) {
+            const int e = from + lane;
+            const uint32_t meta = qm[e];
+            uint32_t sp = qp[e];
+            const int my_first = (int)(meta & 0x1fffffu), my_ns = (int)((meta >> 21) & 15u), my_sidx = (int)(meta >> 25);
+            int32_t prev[3] = {q_prev[warp][0][e], q_prev[warp][1][e], q_prev[warp][2][e]};
+            int32_t cur[3];
+            const uint32_t sizesmall = (uint32_t)c_magic[my_sidx];
+            const int smallnum = (int)(sizesmall >> 1);
+            int a = my_first + 1;
+            if (my_sidx <= 32) {
+                const uint32_t rcpsmall = c_rcp_magic[my_sidx];
+                const int sfull = (my_sidx - 1) >> 3, spart = my_sidx - 8 * sfull;
+                for (int k = 0; k < my_ns; k++, sp += (uint32_t)my_sidx) {
+                    const uint32_t v = (uint32_t)packed_value(peek64(words, nwords, sp), my_sidx, sfull, spart);
+                    uint32_t r2, r1;
+                    const uint32_t qq = divmod32(v, sizesmall, rcpsmall, r2);
+                    const uint32_t q2 = divmod32(qq, sizesmall, rcpsmall, r1);
+                    cur[0] = (int32_t)q2 + prev[0] - smallnum;
+                    cur[1] = (int32_t)r1 + prev[1] - smallnum;
+                    cur[2] = (int32_t)r2 + prev[2] - smallnum;
+                    if (k == 0) {
+                        // the first two atoms of a run are stored in swapped order
+                        emit(my_first, cur[0], cur[1], cur[2]);
+                        emit(a++, prev[0], prev[1], prev[2]);
+                    } else {
+                        emit(a++, cur[0], cur[1], cur[2]);
+                    }
+                    for (int d = 0; d < 3; d++) prev[d] = cur[d];
+                }
             } else {
-                const Triple t = unpack3_wide(bs, bitsize, sizeint[1], sizeint[2]);
-                for (int d = 0; d < 3; d++) cur[d] = t.c[d];
+                BitStream bs;
+                bs.init_at(sbase, send, (int64_t)sp);
+                for (int k = 0; k < my_ns; k++) {
+                    const Triple t = unpack3_wide(bs, my_sidx, sizesmall, sizesmall);
+                    for (int d = 0; d < 3; d++) cur[d] = t.c[d] + prev[d] - smallnum;
+                    if (k == 0) {
+                        emit(my_first, cur[0], cur[1], cur[2]);
+                        emit(a++, prev[0], prev[1], prev[2]);
+                    } else {
+                        emit(a++, cur[0], cur[1], cur[2]);
+                    }
+                    for (int d = 0; d < 3; d++) prev[d] = cur[d];
+                }
             }
         }
-        for (int d = 0; d < 3; d++) cur[d] += minint[d];
-        if (my_ns == 0) {
-            emit(my_first, cur[0], cur[1], cur[2]);
-            continue;
-        }
-        // the flag behind the full-size code, five run bits if it is set, then the small codes
-        uint32_t sp = pos + (uint32_t)bigbits;
-        {
-            const uint32_t w = sp >> 5;
-            const uint32_t fw = w < nwords ? __byte_perm(__ldg(words + w), 0, 0x0123) : 0u;
-            sp += ((fw >> (31 - (sp & 31))) & 1u) ? 6u : 1u;
-        }
-        const uint32_t sizesmall = (uint32_t)c_magic[my_sidx];
-        const int smallnum = (int)(sizesmall >> 1);
-        int32_t prev[3] = {cur[0], cur[1], cur[2]};
-        int a = my_first + 1;
-        if (my_sidx <= 32) {
-            const uint32_t rcpsmall = c_rcp_magic[my_sidx];
-            const int sfull = (my_sidx - 1) >> 3, spart = my_sidx - 8 * sfull;
-            for (int k = 0; k < my_ns; k++, sp += (uint32_t)my_sidx) {
-                const uint32_t v = (uint32_t)packed_value(peek64(words, nwords, sp), my_sidx, sfull, spart);
+    };
+
+    for (int gb = g0; gb < g1; gb += kGroupThreads) {      // whole warps stay in the loop: the queue is theirs
+        const int g = gb + (int)threadIdx.x;
+        bool park = false;
+        uint32_t sp = 0, meta = 0;
+        int32_t cur[3] = {0, 0, 0};
+        if (g < g1) {
+            const uint2 dsc = desc[g];
+            const uint32_t pos = dsc.x;
+            meta = dsc.y;
+            const int my_first = (int)(meta & 0x1fffffu), my_ns = (int)((meta >> 21) & 15u);
+            if (big_fast) {
+                // value = (c0 * s1 + c1) * s2 + c2
+                const uint64_t v = packed_value(peek64(words, nwords, pos), bitsize, bfull, bpart);
                 uint32_t r2, r1;
-                const uint32_t qq = divmod32(v, sizesmall, rcpsmall, r2);
-                const uint32_t q2 = divmod32(qq, sizesmall, rcpsmall, r1);
-                cur[0] = (int32_t)q2 + prev[0] - smallnum;
-                cur[1] = (int32_t)r1 + prev[1] - smallnum;
-                cur[2] = (int32_t)r2 + prev[2] - smallnum;
-                if (k == 0) {
-                    // the first two atoms of a run are stored in swapped order
-                    emit(my_first, cur[0], cur[1], cur[2]);
-                    emit(a++, prev[0], prev[1], prev[2]);
+                const uint64_t qq = divmod64(v, sizeint[2], rcp2, r2);
+                const uint64_t q2 = divmod64(qq, sizeint[1], rcp1, r1);
+                cur[2] = (int32_t)r2; cur[1] = (int32_t)r1; cur[0] = (int32_t)q2;
+            } else {
+                BitStream bs;
+                bs.init_at(sbase, send, (int64_t)pos);
+                if (bitsize == 0) {
+                    for (int d = 0; d < 3; d++) cur[d] = (int32_t)bs.get(bitsint[d]);
                 } else {
-                    emit(a++, cur[0], cur[1], cur[2]);
+                    const Triple t = unpack3_wide(bs, bitsize, sizeint[1], sizeint[2]);
+                    for (int d = 0; d < 3; d++) cur[d] = t.c[d];
                 }
-                for (int d = 0; d < 3; d++) prev[d] = cur[d];
             }
-        } else {
-            BitStream bs;
-            bs.init_at(sbase, send, (int64_t)sp);
-            for (int k = 0; k < my_ns; k++) {
-                const Triple t = unpack3_wide(bs, my_sidx, sizesmall, sizesmall);
-                for (int d = 0; d < 3; d++) cur[d] = t.c[d] + prev[d] - smallnum;
-                if (k == 0) {
-                    emit(my_first, cur[0], cur[1], cur[2]);
-                    emit(a++, prev[0], prev[1], prev[2]);
-                } else {
-                    emit(a++, cur[0], cur[1], cur[2]);
-                }
-                for (int d = 0; d < 3; d++) prev[d] = cur[d];
+            for (int d = 0; d < 3; d++) cur[d] += minint[d];
+            if (my_ns == 0) {
+                emit(my_first, cur[0], cur[1], cur[2]);
+            } else {
+                // the flag behind the full-size code, five run bits if it is set, then the small codes
+                park = true;
+                sp = pos + (uint32_t)bigbits;
+                const uint32_t w = sp >> 5;
+                const uint32_t fw = w < nwords ? __byte_perm(__ldg(words + w), 0, 0x0123) : 0u;
+                sp += ((fw >> (31 - (sp & 31))) & 1u) ? 6u : 1u;
             }
+        }
+        const unsigned parked = __ballot_sync(0xffffffffu, park);
+        if (park) {
+            const int at = queued + __popc(parked & ((1u << lane) - 1u));
+            qp[at] = sp; qm[at] = meta;
+            q_prev[warp][0][at] = cur[0]; q_prev[warp][1][at] = cur[1]; q_prev[warp][2][at] = cur[2];
+        }
+        queued += __popc(parked);
+        __syncwarp();
+        if (queued >= 32) {
+            // the last 32 entries (the queue holds at most 63); what stays is its front
+            decode_runs(queued - 32, 32);
+            __syncwarp();
+            queued -= 32;
         }
     }
+    if (queued > 0) decode_runs(0, queued);
 }
 
 }  // namespace
