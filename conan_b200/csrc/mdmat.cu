@@ -235,7 +235,7 @@ struct MdmatParams {
     int maxlevel;
     int pbc;
     int use_tma;             // 0: stage tiles with plain loads (debug aid, CONAN_MDMAT_NO_TMA=1)
-    int swz;                 // tiles land with the 32-byte TMA swizzle (kpad == 8 only)
+    int swz;                 // tiles land with a TMA swizzle: the 32-byte one for kpad == 8, the 64-byte one for kpad == 16
     int dbg;                 // timing experiments only (CONAN_MDMAT_DEBUG): 1 no exact path, 2 no fill, 4 no items, 8 no pruning
 };
 
@@ -646,6 +646,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         const int nent = counters[0];
         const int nitems = (prm.dbg & 4) ? 0 : nent * nfb;
         const int swz = prm.swz ? 4 : 0;     // 32-byte swizzle: residues 4..7 of every eight have their halves exchanged
+        const int swz16 = (prm.swz && kpad == 16) ? 12 : 0;
         const bool k8 = kpad == 8;
         int gq = 0, qq = tid;      // frame-major walk over (frame, entry): a warp's lanes share the frame,
                                    // so their tile reads fall into different banks
@@ -666,8 +667,8 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                     if (k8)
                         level = fast_pair<PBC, true>(prm, ri, rj, 8 * kTile, swz & i, swz & j, sphI[g * kTile + i],
                                                      sphJ[g * kTile + j], ci, cj, PBC ? boxs + 6 * g : nullptr);
-                    else
-                        level = fast_pair<PBC, false>(prm, ri, rj, pstride, 0, 0, sphI[g * kTile + i],
+                    else   // 64-byte swizzle (kpad == 16): the four 16-byte quarters of a residue's row are permuted by (row / 2) % 4
+                        level = fast_pair<PBC, false>(prm, ri, rj, pstride, swz16 & (i << 1), swz16 & (j << 1), sphI[g * kTile + i],
                                                       sphJ[g * kTile + j], ci, cj, PBC ? boxs + 6 * g : nullptr);
                 }
             }
@@ -897,7 +898,7 @@ const TileMaps* tile_maps(EncodeTiledFn encode, float* base, int kpad, int nres_
     cuuint32_t boxI[4] = {(cuuint32_t)kpad, (cuuint32_t)kTile, (cuuint32_t)kPlanesI, (cuuint32_t)fb};
     cuuint32_t boxJ[4] = {(cuuint32_t)kpad, (cuuint32_t)kTile, (cuuint32_t)kPlanesJ, (cuuint32_t)fb};
     cuuint32_t estr[4] = {1, 1, 1, 1};
-    const CUtensorMapSwizzle sw = swz ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+    const CUtensorMapSwizzle sw = !swz ? CU_TENSOR_MAP_SWIZZLE_NONE : (kpad == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
     tm.base = nullptr;
     CUresult cr = encode(&tm.I, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, boxI, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -1057,7 +1058,7 @@ extern "C" int conan_mdmat_frames_ex(const float* d_xyz, const float* d_box, int
         prm.dbg = d ? atoi(d) : 0;
         const char* z = getenv("CONAN_MDMAT_SWZ");
         const bool want = z ? z[0] == '1' : kDefaultSwz;
-        prm.swz = (want && prm.use_tma && L.kpad == 8) ? 1 : 0;
+        prm.swz = (want && prm.use_tma && (L.kpad == 8 || L.kpad == 16)) ? 1 : 0;
     }
     const int64_t P = symmetric ? (int64_t)nres * (nres - 1) / 2 : (int64_t)xres * yres;
     if (P == 0) return CONAN_OK;
