@@ -241,13 +241,20 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
 
+    def mark(what):      # progress on stderr (CONAN_BENCH_TRACE=1): where a hung run stopped
+        if os.environ.get("CONAN_BENCH_TRACE"):
+            print("[bench rank %d %.1fs] %s" % (rank, time.time() - T0, what), file=sys.stderr, flush=True)
+    T0 = time.time()
+
     nf, nres = args.frames, args.nres
     shard_check = None
     if world > 1:
         # correctness of the sharded path on this many GPUs, before anything is timed
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import sharded_check
+        mark("sharded check")
         shard_check = sharded_check.check(dev)
+        mark("sharded check done")
         ok = torch.tensor([1 if (shard_check is None or shard_check["ok"]) else 0], device=dev)
         dist.broadcast(ok, src=0)
         if not int(ok.item()):
@@ -288,9 +295,11 @@ def run_ours(args):
             launches[0] += 3
 
     # ---- device-resident throughput --------------------------------------------------------
+    mark("resident warm-up")
     for _ in range(max(args.warmup, 3)):
         step_resident()
     barrier()
+    mark("resident timing")
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -414,6 +423,7 @@ def run_ours(args):
         results_home[0] = fetched
 
     results_home = [None]
+    mark("e2e warm-up")
     for _ in range(2):
         step_e2e()
     barrier()
@@ -426,6 +436,7 @@ def run_ours(args):
     b.record(stream)
     barrier()
     ms_e2e = a.elapsed_time(b)
+    mark("e2e done")
 
     # ---- reduce over ranks -----------------------------------------------------------------
     t = torch.tensor([ms, ms_e2e, ms_tile, ms_stats, ms_prep], dtype=torch.float64, device=dev)
@@ -739,7 +750,14 @@ def run_c2(dev):
         f.write("TRAJ %s\nCOORD %s\nNLEVEL 1001\nDT 500\nTRUNC 1.0\nTRUNC_INTER 0.5\nTRUNC_DR 1.0\nDR_MODE init\n"
                 "K_TRAJ_CLUSTERS 1-5\nMATRICES no\nMAKE_MOVIE no\n" % (traj, pdb))
     t0 = time.perf_counter()
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "conan.py"), "fine.inp"], cwd=work, input="2\n", capture_output=True, text=True)
+    # a single-process run of the command line: under torchrun the launcher's variables would make it wait for
+    # ranks that never come
+    env = {k: v for k, v in os.environ.items()
+           if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK", "ROLE_WORLD_SIZE",
+                        "MASTER_ADDR", "MASTER_PORT", "GROUP_WORLD_SIZE", "ROLE_NAME", "OMP_NUM_THREADS")
+           and not k.startswith("TORCHELASTIC_")}
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "conan.py"), "fine.inp"], cwd=work, input="2\n", capture_output=True,
+                       text=True, env=env, timeout=600)
     t_cli = time.perf_counter() - t0
     shutil.rmtree(work, ignore_errors=True)
     return {"workload": "C2: applications/1_ubi_unfold, %d frames x %d pairs (76 residues, 602 heavy atoms), periodic box" % (nf, P),
@@ -828,6 +846,9 @@ def run_config_only(args):
 
 def main():
     args = parse_args()
+    # a run that stops making progress dumps every thread's Python stack and exits instead of holding the GPUs
+    import faulthandler
+    faulthandler.dump_traceback_later(int(os.environ.get("CONAN_BENCH_WATCHDOG", "1500")), exit=True, file=sys.stderr)
     if args.impl == "reference":
         run_reference(args)
     elif args.config:
