@@ -50,11 +50,36 @@ struct PearsonParams {
     int64_t chunk_len;
 };
 
+// Packed FP32 pairs (FFMA2 / FMUL2): two fused multiply-adds per issue slot, each rounded like the scalar one.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// The kernel is bound by instruction issue before it is bound by HBM (a dozen instructions per 2-byte level with
+// four weights), so the sums of a thread's four pairs run as two packed pairs: one FFMA2 per weight and pair of
+// pairs; the weights of a frame sit together in shared memory ([frame][8]) and come with one or two 16-byte
+// reads; eight frames are in flight per thread.
 template <int J>
 __global__ void __launch_bounds__(kThreads) pearson_sums_kernel(const PearsonParams prm) {
-    extern __shared__ float s_mem[];
-    float* s_lut = s_mem;                      // [nlevels]
-    float* s_obs = s_mem + prm.nlevels;        // [J][kWin]
+    extern __shared__ __align__(16) float s_mem[];
+    float* s_obs = s_mem;                      // [kWin][8]
+    float* s_lut = s_mem + kWin * 8;           // [nlevels]
     const int tid = threadIdx.x;
     for (int i = tid; i < prm.nlevels; i += kThreads) s_lut[i] = prm.lut[i];
     const int64_t p0 = ((int64_t)blockIdx.x * kThreads + tid) * kVec;
@@ -64,6 +89,7 @@ __global__ void __launch_bounds__(kThreads) pearson_sums_kernel(const PearsonPar
     float c[kVec];
 #pragma unroll
     for (int q = 0; q < kVec; q++) c[q] = (p0 + q < prm.P) ? prm.shift[p0 + q] : 0.f;
+    const f32x2 nc01 = pack2(-c[0], -c[1]), nc23 = pack2(-c[2], -c[3]), one2 = pack2(1.f, 1.f);
     double accT[J][kVec], accQ[kVec];
 #pragma unroll
     for (int q = 0; q < kVec; q++) {
@@ -76,38 +102,43 @@ __global__ void __launch_bounds__(kThreads) pearson_sums_kernel(const PearsonPar
     for (int64_t fb = fbeg; fb < fend; fb += kWin) {
         const int nblk = (int)min((int64_t)kWin, fend - fb);
         __syncthreads();
-        for (int i = tid; i < J * kWin; i += kThreads) {
-            const int j = i / kWin, fl = i - j * kWin;
-            s_obs[i] = fl < nblk ? prm.obs[(size_t)j * prm.nf + fb + fl] : 0.f;
+        for (int i = tid; i < kWin * 8; i += kThreads) {
+            const int fl = i >> 3, j = i & 7;
+            s_obs[i] = (j < J && fl < nblk) ? prm.obs[(size_t)j * prm.nf + fb + fl] : 0.f;
         }
         __syncthreads();
-        float wT[J][kVec], wQ[kVec];
+        f32x2 wT01[J], wT23[J], wQ01 = 0ull, wQ23 = 0ull;      // (the bit pattern of two +0.0f)
 #pragma unroll
-        for (int q = 0; q < kVec; q++) {
-            wQ[q] = 0.f;
-#pragma unroll
-            for (int j = 0; j < J; j++) wT[j][q] = 0.f;
-        }
-#pragma unroll 4
+        for (int j = 0; j < J; j++) { wT01[j] = 0ull; wT23[j] = 0ull; }
+#pragma unroll 8
         for (int fl = 0; fl < nblk; fl++) {
             const uint2 w = ld_stream(col + (fb + fl) * prm.stride);
-            const unsigned k[kVec] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
-            float o[J];
+            const float4 oa = *reinterpret_cast<const float4*>(s_obs + fl * 8);
+            float4 ob = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (J > 4) ob = *reinterpret_cast<const float4*>(s_obs + fl * 8 + 4);
+            const float o[8] = {oa.x, oa.y, oa.z, oa.w, ob.x, ob.y, ob.z, ob.w};
+            const float v0 = s_lut[min((int)(w.x & 0xffffu), maxk)], v1 = s_lut[min((int)(w.x >> 16), maxk)];
+            const float v2 = s_lut[min((int)(w.y & 0xffffu), maxk)], v3 = s_lut[min((int)(w.y >> 16), maxk)];
+            // d = value - c, as one packed add (x * 1 + (-c) is exact in the product and rounds once, like the subtraction)
+            const f32x2 d01 = fma2(pack2(v0, v1), one2, nc01), d23 = fma2(pack2(v2, v3), one2, nc23);
+            const f32x2 O0 = pack2(o[0], o[0]);
+            wQ01 = fma2(mul2(O0, d01), d01, wQ01);
+            wQ23 = fma2(mul2(O0, d23), d23, wQ23);
 #pragma unroll
-            for (int j = 0; j < J; j++) o[j] = s_obs[j * kWin + fl];
-#pragma unroll
-            for (int q = 0; q < kVec; q++) {
-                const float d = s_lut[min((int)k[q], maxk)] - c[q];
-                wQ[q] = fmaf(o[0] * d, d, wQ[q]);
-#pragma unroll
-                for (int j = 0; j < J; j++) wT[j][q] = fmaf(o[j], d, wT[j][q]);
+            for (int j = 0; j < J; j++) {
+                const f32x2 Oj = pack2(o[j], o[j]);
+                wT01[j] = fma2(Oj, d01, wT01[j]);
+                wT23[j] = fma2(Oj, d23, wT23[j]);
             }
         }
+        float q0, q1, q2, q3;
+        unpack2(wQ01, q0, q1); unpack2(wQ23, q2, q3);
+        accQ[0] += (double)q0; accQ[1] += (double)q1; accQ[2] += (double)q2; accQ[3] += (double)q3;
 #pragma unroll
-        for (int q = 0; q < kVec; q++) {
-            accQ[q] += (double)wQ[q];
-#pragma unroll
-            for (int j = 0; j < J; j++) accT[j][q] += (double)wT[j][q];
+        for (int j = 0; j < J; j++) {
+            float t0, t1, t2, t3;
+            unpack2(wT01[j], t0, t1); unpack2(wT23[j], t2, t3);
+            accT[j][0] += (double)t0; accT[j][1] += (double)t1; accT[j][2] += (double)t2; accT[j][3] += (double)t3;
         }
     }
 #pragma unroll
@@ -273,7 +304,7 @@ extern "C" int conan_pearson_sums(const uint16_t* d_levels, int64_t levels_strid
     clen = (clen + kWin - 1) / kWin * kWin;
     nchunks = (nf + clen - 1) / clen;
     prm.chunk_len = clen;
-    const size_t smem = sizeof(float) * ((size_t)nlevels + (size_t)J * kWin);
+    const size_t smem = sizeof(float) * ((size_t)nlevels + (size_t)8 * kWin);
     dim3 grid((unsigned)tiles, (unsigned)nchunks);
 #define CONAN_LAUNCH_PEARSON(JJ)                                                                              \
     case JJ:                                                                                                   \
