@@ -303,6 +303,15 @@ __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, co
     {
         const f32x2 M2 = pack2(-2.f, -2.f);
         const f32x2 DX = pack2(Dx2, Dx2), DY = pack2(Dy2, Dy2), DZ = pack2(Dz2, Dz2);
+        if (ICH == 2) {      // one packed pair: an 8-byte read per plane (the swizzle moves whole 16-byte quarters)
+            const int o = a0 ^ xi;
+            const float2 qx = *reinterpret_cast<const float2*>(aI + o);
+            const float2 qy = *reinterpret_cast<const float2*>(aI + pstride + o);
+            const float2 qz = *reinterpret_cast<const float2*>(aI + 2 * pstride + o);
+            tx[0] = fma2(pack2(qx.x, qx.y), M2, DX);
+            ty[0] = fma2(pack2(qy.x, qy.y), M2, DY);
+            tz[0] = fma2(pack2(qz.x, qz.y), M2, DZ);
+        }
 #pragma unroll
         for (int v = 0; v < ICH / 4; v++) {
             const int o = (a0 + 4 * v) ^ xi;
@@ -340,7 +349,7 @@ __device__ __forceinline__ float chunk_min_fast(const float* __restrict__ aI, co
                 mu[2 * u + 1] = fmin3(mu[2 * u + 1], b1, c1);
             }
         }
-        {
+        if (K8 || b + 2 < cj) {      // (generic sizes: the second half of the last trip may hold padding only)
             const f32x2 BX = pack2(bx.z, bx.z), BY = pack2(by.z, by.z), BZ = pack2(bz.z, bz.z), NB = pack2(bn.z, bn.z);
             const f32x2 CX = pack2(bx.w, bx.w), CY = pack2(by.w, by.w), CZ = pack2(bz.w, bz.w), NC = pack2(bn.w, bn.w);
 #pragma unroll
@@ -446,9 +455,11 @@ __device__ __forceinline__ int fast_pair(const MdmatParams& prm, const float* __
         if (ci > 4) m = chunk_min_fast<8, true>(aIp, aJp, pstride, 0, xi, xj, cj, Dx2, Dy2, Dz2, m);
         else m = chunk_min_fast<4, true>(aIp, aJp, pstride, 0, xi, xj, cj, Dx2, Dy2, Dz2, m);
     } else {
+        // row atoms in chunks of 8, then what is left in a chunk of 8 (7-8 atoms), 4 (+ 2) or 2
         int a0 = 0;
-        while (ci - a0 > 4) { m = chunk_min_fast<8, false>(aIp, aJp, pstride, a0, xi, xj, cj, Dx2, Dy2, Dz2, m); a0 += 8; }
-        if (ci - a0 > 0) m = chunk_min_fast<4, false>(aIp, aJp, pstride, a0, xi, xj, cj, Dx2, Dy2, Dz2, m);
+        while (ci - a0 > 6) { m = chunk_min_fast<8, false>(aIp, aJp, pstride, a0, xi, xj, cj, Dx2, Dy2, Dz2, m); a0 += 8; }
+        if (ci - a0 > 2) { m = chunk_min_fast<4, false>(aIp, aJp, pstride, a0, xi, xj, cj, Dx2, Dy2, Dz2, m); a0 += 4; }
+        if (ci - a0 > 0) m = chunk_min_fast<2, false>(aIp, aJp, pstride, a0, xi, xj, cj, Dx2, Dy2, Dz2, m);
     }
     const float mm = fmaxf(m, 0.f);
     // sqrt through the reciprocal square root (2^-22.9 relative) instead of the IEEE sequence; the
