@@ -284,11 +284,28 @@ def run_ours(args):
 
     launches = [0]
 
+    # The merge behind a shard's pass (packing kernels and two all-reduces, all small) runs on a stream of its own,
+    # so the next step's distance kernel does not queue behind it; the pass of the next step waits for it (it
+    # rewrites `out`), and so does the end of every timed region.
+    merge_stream = torch.cuda.Stream(dev) if world > 1 else None
+    merged = [None]
+
+    def sharded_stats():
+        if merged[0] is not None:
+            stream.wait_event(merged[0])
+        st = sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2,
+                                        merge_stream=merge_stream)
+        merged[0] = st.merged
+
+    def join_merge():
+        if merged[0] is not None:
+            stream.wait_event(merged[0])
+
     def step_resident():
         stage1.mdmat_frames(d_xyz, None, geom, TRUNC, NLEVELS, False, levels, work1, counters)
         launches[0] += 2
         if world > 1:
-            sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
+            sharded_stats()
             launches[0] += 4           # shard summary + entering status + streaming pass + combine (collectives are NCCL's)
         else:
             stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2)
@@ -309,6 +326,7 @@ def run_ours(args):
     e0.record(stream)
     for _ in range(args.steps):
         step_resident()
+    join_merge()                 # the timed region ends when the last step's merge has finished
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
@@ -408,7 +426,8 @@ def run_ours(args):
         if results_home[0] is not None:
             stream.wait_event(results_home[0])      # the previous step's results have left `out`
         if world > 1:
-            sharded.pair_stats_sharded(levels, P, NLEVELS, lo, hi, eq, frame0=rank * nf, out=out, work=work2)
+            sharded_stats()
+            join_merge()                     # (the results that go home are the merged ones)
         else:
             stage2.pair_stats(levels, P, NLEVELS, lo, hi, eq, out=out, work=work2)
         # the results go home on a stream of their own, so the next step's kernels do not queue behind the transfer

@@ -32,17 +32,28 @@ def exchange_summaries(first_row_local, last_row_local, decided, status_out, gro
     P = decided.numel()
     u8 = lambda t: t.contiguous().view(torch.uint8).reshape(-1)         # the collectives have no 16-bit unsigned type
     rec = torch.cat([u8(first_row_local[:P]), u8(last_row_local[:P]), u8(decided), u8(status_out)])
-    recs = [torch.empty_like(rec) for _ in range(world)]
-    dist.all_gather(recs, rec, group=group)
-    row = lambda r, k: recs[r][2 * P * k:2 * P * (k + 1)].view(first_row_local.dtype)
-    dec = lambda r: recs[r][4 * P:5 * P]
-    sta = lambda r: recs[r][5 * P:6 * P]
-    s_in = torch.zeros_like(status_out)
-    for q in range(rank):
-        s_in = torch.where(dec(q) != 0, sta(q), s_in)
-    s_end = s_in
-    for q in range(rank, world):
-        s_end = torch.where(dec(q) != 0, sta(q), s_end)
+    if rec.is_cuda:
+        recs = torch.empty((world, rec.numel()), dtype=torch.uint8, device=rec.device)
+        dist.all_gather_into_tensor(recs, rec, group=group)
+    else:       # (gloo, CPU tests)
+        parts = [torch.empty_like(rec) for _ in range(world)]
+        dist.all_gather(parts, rec, group=group)
+        recs = torch.stack(parts)
+    row = lambda r, k: recs[r, 2 * P * k:2 * P * (k + 1)].view(first_row_local.dtype)
+    dec, sta = recs[:, 4 * P:5 * P], recs[:, 5 * P:6 * P]
+
+    def last_decided(n, start):
+        """status left behind by the last of the shards 0..n-1 that has a frame outside the buffer, else `start`."""
+        if n == 0:
+            return start
+        order = torch.arange(1, n + 1, dtype=torch.int16, device=recs.device)[:, None]
+        which = torch.where(dec[:n] != 0, order, torch.zeros_like(order)).amax(0)          # 0: none of them
+        picked = sta[:n].gather(0, (which.long() - 1).clamp_(min=0)[None])[0]
+        return torch.where(which > 0, picked, start)
+
+    zero = torch.zeros_like(status_out)
+    s_in = last_decided(rank, zero)
+    s_end = last_decided(world, zero)
     return row(0, 0), (row(rank - 1, 1) if rank > 0 else None), s_in, s_end
 
 
@@ -71,12 +82,16 @@ def merge_pair_stats(st, final_status=None, group=None):
 
 
 def pair_stats_sharded(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0, out=None, work=None, group=None,
-                       local_pass=None, local_summary=None):
+                       local_pass=None, local_summary=None, merge_stream=None):
     """Stage 2 over this rank's frame shard, merged so that per-pair results equal a single run: one all-gather
     before the streaming pass, two all-reduces after it.
 
     Per-frame results stay local to the rank (frames are disjoint).  `local_pass` / `local_summary`
-    exist for the CPU tests: callables with the signatures of stage2.pair_stats / shard_summary."""
+    exist for the CPU tests: callables with the signatures of stage2.pair_stats / shard_summary.
+    merge_stream: a CUDA stream on which the merge after the pass runs (its packing kernels and the two
+    all-reduces are small and latency-bound; a caller that goes straight on to the next shard's distances hides
+    them behind that kernel).  The result then carries an event `merged`: wait for it before reading the per-pair
+    fields or reusing `out`."""
     if local_pass is None:
         from . import stage2
         local_pass, local_summary = stage2.pair_stats, stage2.shard_summary
@@ -86,7 +101,18 @@ def pair_stats_sharded(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0, 
     pad = lambda r: None if r is None else torch.nn.functional.pad(r.view(torch.int16), (0, levels.shape[1] - P)).view(levels.dtype)
     st = local_pass(levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=frame0, first_row=pad(first_row),
                     prev_row=pad(prev_row), status_in=s_in, out=out, work=work)
-    return merge_pair_stats(st, s_end, group)
+    if merge_stream is None:
+        return merge_pair_stats(st, s_end, group)
+    passed = torch.cuda.Event()
+    passed.record(torch.cuda.current_stream(levels.device))
+    with torch.cuda.stream(merge_stream):
+        merge_stream.wait_event(passed)
+        merge_pair_stats(st, s_end, group)
+        st.merged = torch.cuda.Event()
+        st.merged.record(merge_stream)
+    for t in (s_end, st.decided):
+        t.record_stream(merge_stream)
+    return st
 
 
 # ------------------------------------------------------------------------------------------------

@@ -52,8 +52,17 @@ def check(dev, verbose=False):
         return levels
 
     mine = buffered(mine, f0)
+    # once with the merge on a stream of its own (what the step loop of bench.py does), once in line: same numbers
+    side = torch.cuda.Stream(dev)
+    st2 = sharded.pair_stats_sharded(mine, P, nlevels, lo, hi, eq, frame0=f0, merge_stream=side)
+    st2.merged.synchronize()
     st = sharded.pair_stats_sharded(mine, P, nlevels, lo, hi, eq, frame0=f0)
     torch.cuda.synchronize(dev)
+    same_on_side_stream = all(bool(torch.equal(getattr(st, n), getattr(st2, n)))
+                              for n in ("sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f", "status", "decided"))
+    flag = torch.tensor([1 if same_on_side_stream else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    same_on_side_stream = bool(int(flag.item()))
     # the per-frame outputs of all ranks on rank 0
     sizes = [min(nf, (r + 1) * per) - r * per for r in range(world)]
     frame_fields = {}
@@ -73,7 +82,8 @@ def check(dev, verbose=False):
         bad += [k for k, v in frame_fields.items() if not np.array_equal(v, ref[k])]
         carried = int((ref["n_int"][::18] >= min(nf, int(2.5 * per))).sum())      # pairs that stayed on through the buffer
         rec = {"world": world, "frames": nf, "pairs": P, "stage2": "bit-exact" if not bad else "MISMATCH: " + ",".join(bad),
-               "status_carried_across_shards": carried, "n_enc_max": int(ref["n_enc"].max())}
+               "status_carried_across_shards": carried, "n_enc_max": int(ref["n_enc"].max()),
+               "merge_on_side_stream": "same" if same_on_side_stream else "DIFFERENT"}
         if verbose:
             print("stage 2 shards:", rec)
 
@@ -104,7 +114,7 @@ def check(dev, verbose=False):
         e_np = np.linalg.norm(cov.cpu().numpy() - np.cov(vec)) / np.linalg.norm(np.cov(vec))
         rec.update({"mean_max_abs_diff": float(np.abs(full_mean - mean).max()), "cov_rel_frob": e_cov,
                     "cov_rel_frob_vs_numpy_f64": float(e_np), "ff_rel_frob": e_d, "stage3_pairs": int(len(sel))})
-        rec["ok"] = bool(rec["stage2"] == "bit-exact" and nf_total == nf and rec["mean_max_abs_diff"] < 1e-12 and
+        rec["ok"] = bool(rec["stage2"] == "bit-exact" and same_on_side_stream and nf_total == nf and rec["mean_max_abs_diff"] < 1e-12 and
                          e_cov < 2e-6 and e_d < 2e-6 and e_np < 1e-5 and carried > 0)
         if verbose:
             print("stage 3 shards:", {k: rec[k] for k in ("cov_rel_frob", "cov_rel_frob_vs_numpy_f64", "ff_rel_frob", "stage3_pairs")})
