@@ -32,10 +32,10 @@ def exchange_summaries(first_row_local, last_row_local, decided, status_out, gro
     P = decided.numel()
     u8 = lambda t: t.contiguous().view(torch.uint8).reshape(-1)         # the collectives have no 16-bit unsigned type
     rec = torch.cat([u8(first_row_local[:P]), u8(last_row_local[:P]), u8(decided), u8(status_out)])
-    if rec.is_cuda:
+    if dist.get_backend(group) == "nccl":
         recs = torch.empty((world, rec.numel()), dtype=torch.uint8, device=rec.device)
-        dist.all_gather_into_tensor(recs, rec, group=group)
-    else:       # (gloo, CPU tests)
+        dist.all_gather_into_tensor(recs.view(-1), rec, group=group)
+    else:       # (gloo: the CPU tests, several ranks on one GPU)
         parts = [torch.empty_like(rec) for _ in range(world)]
         dist.all_gather(parts, rec, group=group)
         recs = torch.stack(parts)
