@@ -241,7 +241,7 @@ def pca(ctx, npc):
 def get_best_center(cluster, dist_rows):
     """Medoid: the member with the smallest summed distance to the others (conan.py:1172-1185)."""
     sub = dist_rows[np.ix_(cluster, cluster)]
-    return int(cluster[int(np.argmin(sub.sum(axis=1)))])
+    return int(cluster[int(np.argmin(sub.sum(axis=1, dtype=np.float64)))])
 
 
 def cluster_trajectory(ctx, ks, trunc, trunc_inter, asymm):
@@ -258,7 +258,9 @@ def cluster_trajectory(ctx, ks, trunc, trunc_inter, asymm):
     D.fill_diagonal_(0.0)
     print("Done.")
     nf = ctx.nf
-    Dh = D.cpu().numpy().astype(np.float64)
+    # The matrix stays float32 on the host (1.6 GB at 20 000 frames, not 3.2); only what scipy needs -- the condensed
+    # upper triangle -- is widened, and sums over it are taken in float64.
+    Dh = D.cpu().numpy()
     delta = int(nf / 1000) if nf > 1000 else 1
     if nf > 1000:
         print("There are more than 1000 frames, we will limit the interframe plots to approx. 1000x1000.")
@@ -268,9 +270,10 @@ def cluster_trajectory(ctx, ks, trunc, trunc_inter, asymm):
             f.write("".join("%8.3f %8.3f %12.6f\n" % (tn[i], tn[j], Dh[i, j]) for j in range(0, nf, delta)))
             f.write("\n")
     print("hierarchical...")
-    iu = np.triu_indices(nf, 1)
-    cond = Dh[iu]
+    from scipy.spatial.distance import squareform
+    cond = squareform(Dh, checks=False).astype(np.float64)      # (the GPU result is symmetric, with a zero diagonal)
     Z = linkage(cond, 'ward')
+    del cond
     with open("cluster_trj/linkage.txt", "w") as f:
         for row in Z:
             f.write("%6i %6i %12.6f %6i\n" % tuple(row))
