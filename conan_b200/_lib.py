@@ -74,6 +74,10 @@ SIGNATURES = {
                                         c_i32, c_void_p, c_void_p, c_void_p,
                                         ctypes.POINTER(PairStatsOut), ctypes.POINTER(FrameStatsOut),
                                         c_void_p, c_size, c_void_p]),
+    "conan_pair_stats_ex": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32,
+                                        c_i32, c_void_p, c_void_p, c_void_p,
+                                        ctypes.POINTER(PairStatsOut), ctypes.POINTER(FrameStatsOut),
+                                        c_void_p, c_size, c_i32, c_void_p]),
     "conan_dimer_orient": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i32, c_i32, c_void_p, c_void_p]),
     "conan_dimer_ssd": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "conan_pearson_sums": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_void_p, c_i32, c_void_p, c_i32,

@@ -25,6 +25,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "common.h"
 
@@ -61,6 +62,7 @@ struct StatsParams {
     int nchunks;
     int lo_cnt, hi_first;
     int one;                      // == 1, opaque to the compiler: k*one - kp becomes one IMAD on the FMA pipe
+    unsigned quiet_word;          // QUIET kernels: two packed copies of the last level
     const uint16_t* first_row;    // levels of global frame 0
     const uint16_t* prev_row;     // levels of the frame before local frame 0 (may be null)
     const uint8_t* status_in;     // status entering local frame 0 (may be null = off)
@@ -211,7 +213,12 @@ __device__ __forceinline__ void frame_step(unsigned wx, unsigned wy, unsigned c_
     }
 }
 
-template <bool MASKED, bool WIDE>
+// QUIET: stages (8 frames) in which all of the warp's 128 pairs sit at the last level, as they did in the frame
+// before, are only counted -- nobody is on, the differences to the previous frame are zero, the one to the first
+// frame is the same every time -- and the history masks and level sums catch up at the next busy stage or when the
+// window closes.  Pays on sparse, block-structured stacks (an X x Y interface, multi-domain proteins); on a stack
+// whose every 128-pair stretch holds something the test is pure overhead, hence a separate instantiation.
+template <bool MASKED, bool WIDE, bool QUIET>
 __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s_part)[kThreads / 32][kWin],
                                            unsigned (*s_hi0)[kThreads / 32][kWin], const uint16_t* s_rows,
                                            uint64_t* full_bar, uint64_t* empty_bar) {
@@ -275,6 +282,23 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
         n_int[q] = 0; n_enc[q] = 0; first_f[q] = -1; last_f[q] = -1;
     }
 
+    // quiet stages: what a frame of nothing but last levels adds to the per-frame sums of this warp
+    const unsigned qw = prm.quiet_word, ql = qw & 0xffffu;
+    uint4 quiet_part = make_uint4(0, 0, 0, 0);
+    unsigned quiet_hi0 = 0;
+    int nq = 0, nq_win = 0;
+    if (QUIET && !MASKED) {
+        unsigned s0 = 0;
+#pragma unroll
+        for (int q = 0; q < kVec; q++) { const int d0 = (int)ql - (int)k0[q]; s0 += (unsigned)(d0 * d0); }
+        if (!WIDE) {
+            quiet_part.z = __reduce_add_sync(0xffffffffu, s0);
+        } else {
+            quiet_part.z = __reduce_add_sync(0xffffffffu, s0 & 0xffffu);
+            quiet_hi0 = __reduce_add_sync(0xffffffffu, s0 >> 16);
+        }
+    }
+
     // this thread's four levels of frame r of stage slot: 8 bytes at a fixed offset
     const uint16_t* my = s_rows + tid * kVec;
     int it = 0, buf = 0;      // it: stage iteration since the start of the chunk
@@ -288,14 +312,49 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
             mbar_wait(&full_bar[slot], (uint32_t)(it / kStagesS) & 1u);
             const uint16_t* rows = my + (size_t)slot * kStageFrames * kPairsPerCta;
             if (nblk - u0 >= kStageFrames) {
+                bool all_quiet = false;
+                if (QUIET && !MASKED) {
+                    unsigned diff = (on_x | on_y) & 0x80008000u;
 #pragma unroll
-                for (int u = 0; u < kStageFrames; u++) {
-                    uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
-                    if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
-                    frame_step<WIDE>(w.x, w.y, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
-                                     slots + u0 + u, slots_hi0 + u0 + u, lane0, prm.one);
+                    for (int q = 0; q < kVec; q++) diff |= kp[q] ^ ql;
+#pragma unroll
+                    for (int u = 0; u < kStageFrames; u++) {
+                        const uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
+                        diff |= (w.x ^ qw) | (w.y ^ qw);
+                    }
+                    all_quiet = __all_sync(0xffffffffu, diff == 0);
+                }
+                if (QUIET && all_quiet) {
+                    nq += kStageFrames;
+                    if (lane0) {
+#pragma unroll
+                        for (int u = 0; u < kStageFrames; u++) {
+                            *reinterpret_cast<uint4*>(slots + u0 + u) = quiet_part;
+                            if (WIDE) slots_hi0[u0 + u] = quiet_hi0;
+                        }
+                    }
+                } else {
+                    if (QUIET && nq) {
+#pragma unroll
+                        for (int q = 0; q < kVec; q++) hist[q] = nq < 32 ? hist[q] << nq : 0u;
+                        nq_win += nq;
+                        nq = 0;
+                    }
+#pragma unroll
+                    for (int u = 0; u < kStageFrames; u++) {
+                        uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
+                        if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
+                        frame_step<WIDE>(w.x, w.y, c_lo, c_hi, valid_y, native_y, on_x, on_y, hist, a1, a2, kp, k0,
+                                         slots + u0 + u, slots_hi0 + u0 + u, lane0, prm.one);
+                    }
                 }
             } else {   // the last, partial stage of the call
+                if (QUIET && nq) {
+#pragma unroll
+                    for (int q = 0; q < kVec; q++) hist[q] = nq < 32 ? hist[q] << nq : 0u;
+                    nq_win += nq;
+                    nq = 0;
+                }
                 for (int u = 0; u < nblk - u0; u++) {
                     uint2 w = *reinterpret_cast<const uint2*>(rows + u * kPairsPerCta);
                     if (MASKED) { w.x &= mask_x; w.y &= mask_y; }
@@ -309,6 +368,19 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
         // close the window: counts from the history masks, widen the 32-bit sums (nlevels <= 7744
         // keeps 32 frames of k^2 below 2^31)
         const int wbase = (int)(prm.frame0 + fb);
+        if (QUIET) {
+            if (nq) {
+#pragma unroll
+                for (int q = 0; q < kVec; q++) hist[q] = nq < 32 ? hist[q] << nq : 0u;
+                nq_win += nq;
+                nq = 0;
+            }
+            if (nq_win) {     // the quiet stages' share of the level sums
+#pragma unroll
+                for (int q = 0; q < kVec; q++) { a1[q] += (unsigned)nq_win * ql; a2[q] += (unsigned)nq_win * ql * ql; }
+                nq_win = 0;
+            }
+        }
 #pragma unroll
         for (int q = 0; q < kVec; q++) {
             close_window(hist[q], nblk, (carry >> q) & 1u, wbase, n_int[q], n_enc[q], first_f[q], last_f[q]);
@@ -357,7 +429,7 @@ __device__ __forceinline__ void stats_body(const StatsParams& prm, FramePart (*s
     }
 }
 
-template <bool WIDE>
+template <bool WIDE, bool QUIET>
 __global__ void __launch_bounds__(kThreads + 32, 2) pair_stats_kernel(const StatsParams prm) {
     extern __shared__ __align__(128) unsigned char s_dyn[];    // [kStagesS][kStageFrames][1024] levels
     __shared__ __align__(16) FramePart s_part[2][kThreads / 32][kWin];   // per-warp, per-frame partial sums
@@ -392,8 +464,8 @@ __global__ void __launch_bounds__(kThreads + 32, 2) pair_stats_kernel(const Stat
     }
     // only the last pair tile can contain padding columns
     const bool tail = ((int64_t)(blockIdx.x + 1) * kPairsPerCta > prm.P);
-    if (tail) stats_body<true, WIDE>(prm, s_part, s_hi0, s_rows, full_bar, empty_bar);
-    else stats_body<false, WIDE>(prm, s_part, s_hi0, s_rows, full_bar, empty_bar);
+    if (tail) stats_body<true, WIDE, QUIET>(prm, s_part, s_hi0, s_rows, full_bar, empty_bar);
+    else stats_body<false, WIDE, QUIET>(prm, s_part, s_hi0, s_rows, full_bar, empty_bar);
 }
 
 struct CombineParams {
@@ -494,6 +566,18 @@ extern "C" int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride,
                                 const uint8_t* d_status_in, const conan_pair_stats_out* out,
                                 const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
                                 void* stream_) {
+    const char* e = getenv("CONAN_STATS_SPARSE");
+    return conan_pair_stats_ex(d_levels, levels_stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut, d_first_row,
+                               d_prev_row, d_status_in, out, fout, d_work, work_bytes, (e && atoi(e) != 0) ? CONAN_STATS_SPARSE : 0,
+                               stream_);
+}
+
+extern "C" int conan_pair_stats_ex(const uint16_t* d_levels, int64_t levels_stride, int64_t nf, int64_t P,
+                                   int64_t frame0, int32_t nlevels, int32_t lo_cnt, int32_t hi_first,
+                                   int32_t equal_cut, const uint16_t* d_first_row, const uint16_t* d_prev_row,
+                                   const uint8_t* d_status_in, const conan_pair_stats_out* out,
+                                   const conan_frame_stats_out* fout, void* d_work, size_t work_bytes,
+                                   int32_t flags, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (!out || !fout || !d_work) return conan::fail(CONAN_ERR_ARG, "conan_pair_stats: null pointer argument");
     if (!out->d_sum_k || !out->d_sum_k2 || !out->d_n_int || !out->d_n_enc || !out->d_first_f ||
@@ -551,13 +635,21 @@ extern "C" int conan_pair_stats(const uint16_t* d_levels, int64_t levels_stride,
     CONAN_CUDA_TRY(cudaGetLastError());
     dim3 grid((unsigned)tiles, (unsigned)pl.nchunks);
     const size_t smem = (size_t)kStagesS * kStageFrames * kPairsPerCta * sizeof(uint16_t);
+    // The sparse variant skips stages of nothing but last levels; it needs a pair at the last level to be off
+    // whatever it was before, i.e. the last level at or above both cut-offs (else it is not used).
+    const bool sparse = (flags & CONAN_STATS_SPARSE) && nlevels - 1 >= hi_first && nlevels - 1 >= lo_cnt;
+    sp.quiet_word = sparse ? (unsigned)(nlevels - 1) * 0x00010001u : 0u;
+#define CONAN_LAUNCH_STATS(W, Q)                                                                                       \
+    do {                                                                                                                \
+        CONAN_CUDA_TRY(cudaFuncSetAttribute(pair_stats_kernel<W, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        pair_stats_kernel<W, Q><<<grid, kThreads + 32, smem, stream>>>(sp);                                           \
+    } while (0)
     if (nlevels <= kSmallLevels) {
-        CONAN_CUDA_TRY(cudaFuncSetAttribute(pair_stats_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        pair_stats_kernel<false><<<grid, kThreads + 32, smem, stream>>>(sp);
+        if (sparse) CONAN_LAUNCH_STATS(false, true); else CONAN_LAUNCH_STATS(false, false);
     } else {
-        CONAN_CUDA_TRY(cudaFuncSetAttribute(pair_stats_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        pair_stats_kernel<true><<<grid, kThreads + 32, smem, stream>>>(sp);
+        if (sparse) CONAN_LAUNCH_STATS(true, true); else CONAN_LAUNCH_STATS(true, false);
     }
+#undef CONAN_LAUNCH_STATS
     CONAN_CUDA_TRY(cudaGetLastError());
 
     CombineParams cp;

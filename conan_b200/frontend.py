@@ -288,6 +288,7 @@ def distributed():
 
 _last_stage1 = None   # handed from mdmat_run to read_process_frames within one process
 XPM_WRITE_LIMIT = 2.0e8   # level entries above which dmf.xpm is not written unless WRITE_XPM yes
+SPARSE_STACK_BELOW = 0.04  # stage 2 takes its sparse variant when fewer than this share of the entries survived stage 1's pruning
 
 
 def select_frames(times, begin, end, dt):
@@ -481,6 +482,9 @@ def mdmat_run(program, traj, coord, nlevels, trunc, mean, begin, end, dt, indexf
     print("Computed %d distance matrices of %d residues (%d results within 2 ulp of a level boundary)."
           % (len(all_frames), geom.nres, nb))
     _last_stage1 = Stage1Result(levels, geom, x.times[all_frames], trunc, nlevels, nb, shard)
+    # the share of (residue pair, frame) entries that passed the bounding-sphere pruning: tells stage 2 whether the
+    # stack is sparse enough for its variant that skips stretches of nothing but last levels
+    _last_stage1.survivor_frac = float(counters[1].item()) / max(1.0, float(geom.P) * len(all_frames))
     entries = float(len(all_frames)) * geom.nres * geom.nres
     if world > 1:
         write_xpm = bool(write_xpm) and False      # the stack is spread over the GPUs: no dmf.xpm (WRITE_XPM is ignored)
@@ -869,7 +873,8 @@ def read_process_frames(inputf, nres, nlevels, nchar, dict_legend, asymm_data, t
             return None            # rank 0 holds the merged statistics and the whole stack from here on
         nf = d_stack.shape[0]
     else:
-        stats = stage2.pair_stats(d_stack, P, nlevels, lo, hi, eq).host()
+        frac = getattr(_last_stage1, "survivor_frac", None) if _last_stage1 is not None else None
+        stats = stage2.pair_stats(d_stack, P, nlevels, lo, hi, eq, sparse=(frac < SPARSE_STACK_BELOW) if frac is not None else None).host()
     if dimer:
         # rmsd_frame's dimer branch (:1420-1428): the smaller of the distance to a frame and to its transpose
         tp = torch.zeros(nf, dtype=torch.int64, device=dev)

@@ -46,8 +46,10 @@ def pair_stats_workspace_bytes(nf, P):
 
 
 def pair_stats(d_levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=0, first_row=None, prev_row=None,
-               status_in=None, out=None, work=None, stream=None):
-    """Launch stage 2 on a device level stack [nf, stride] (uint16); returns PairStats (device)."""
+               status_in=None, out=None, work=None, stream=None, sparse=None):
+    """Launch stage 2 on a device level stack [nf, stride] (uint16); returns PairStats (device).
+    sparse=True: the variant that skips 8-frame stages of nothing but last levels (same results; for stacks in which
+    few pairs ever come within trunc); None: the library's default (environment variable CONAN_STATS_SPARSE)."""
     lib = _lib.load()
     if not d_levels.is_cuda:
         raise _lib.ConanError(-1, "stage 2 needs device tensors: there is no CPU fallback")
@@ -61,9 +63,14 @@ def pair_stats(d_levels, P, nlevels, lo_cnt, hi_first, equal_cut, frame0=0, firs
     fo = _lib.FrameStatsOut(*[getattr(out, n).data_ptr() for n, _ in PairStats.FRAME_FIELDS])
     s = stream if stream is not None else torch.cuda.current_stream(dev)
     ptr = lambda t: 0 if t is None else t.data_ptr()
-    _lib.check(lib.conan_pair_stats(d_levels.data_ptr(), stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
-                                    ptr(first_row), ptr(prev_row), ptr(status_in), ctypes.byref(po), ctypes.byref(fo),
-                                    work.data_ptr(), work.numel(), s.cuda_stream))
+    if sparse is None:
+        _lib.check(lib.conan_pair_stats(d_levels.data_ptr(), stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
+                                        ptr(first_row), ptr(prev_row), ptr(status_in), ctypes.byref(po), ctypes.byref(fo),
+                                        work.data_ptr(), work.numel(), s.cuda_stream))
+    else:
+        _lib.check(lib.conan_pair_stats_ex(d_levels.data_ptr(), stride, nf, P, frame0, nlevels, lo_cnt, hi_first, equal_cut,
+                                           ptr(first_row), ptr(prev_row), ptr(status_in), ctypes.byref(po), ctypes.byref(fo),
+                                           work.data_ptr(), work.numel(), 1 if sparse else 0, s.cuda_stream))
     out.work = work
     out._keepalive = (first_row, prev_row, status_in)
     return out

@@ -8,6 +8,14 @@ PAIR_KEYS = ("sum_k", "sum_k2", "n_int", "n_enc", "first_f", "last_f", "status")
 FRAME_KEYS = ("native", "nonnative", "ssd_prev", "ssd_first")
 
 
+@pytest.fixture(autouse=True, params=["dense", "sparse"])
+def stats_variant(request, monkeypatch):
+    """Every test runs under both variants of the streaming pass: the default one and the one that skips 8-frame
+    stages of nothing but last levels (conan_pair_stats takes the flag from CONAN_STATS_SPARSE)."""
+    monkeypatch.setenv("CONAN_STATS_SPARSE", "1" if request.param == "sparse" else "0")
+    return request.param
+
+
 def _device_stack(levels):
     import torch
     from conan_b200.levels import padded_stride
@@ -147,3 +155,29 @@ def test_bad_arguments_are_errors(lib):
         stage2.pair_stats(d, 100, 101, 50, 60, 0)            # P larger than the row pitch
     with pytest.raises(ConanError):
         stage2.pair_stats(d.cpu(), 10, 101, 50, 60, 0)       # host tensor: no CPU path
+
+
+@pytest.mark.parametrize("nlevels,lo,hi", [(1001, 500, 601), (7744, 3000, 5000), (41, 20, 24)])
+def test_sparse_block_structured_stack(lib, orc, nlevels, lo, hi):
+    """Mostly last levels, with contact patches that come and go: whole 128-pair stretches are quiet for many
+    stages, quiet stages sit between busy ones inside a window, patches switch on right after a quiet stage and
+    windows end in the middle of quiet runs.  Both variants must give the oracle's numbers."""
+    from conan_b200 import stage2
+    rng = np.random.default_rng(nlevels)
+    nf, P = 1000, 6000
+    levels = np.full((nf, P), nlevels - 1, np.uint16)
+    for _ in range(60):
+        p0, w = int(rng.integers(0, P - 40)), int(rng.integers(1, 40))
+        f0, d = int(rng.integers(0, nf - 5)), int(rng.integers(1, 300))
+        patch = rng.integers(0, nlevels, size=(min(d, nf - f0), w))
+        levels[f0:f0 + d, p0:p0 + w] = patch
+    levels[0, 3000:3128] = lo // 2            # on in the first frame only: the status must be dropped, not carried
+    levels[8:16, 4096:4224] = nlevels - 1     # (already quiet) one stage of a stretch
+    levels[16, 4100] = 0                      # a contact right after a quiet stage
+    levels[nf - 1, 5000] = 0                  # and in the last frame
+    want = orc.pair_stats(levels, lo, hi, 0)
+    got = stage2.pair_stats(_device_stack(levels), P, nlevels, lo, hi, 0).host()
+    _check(got, want)
+    # the explicit flag gives the same as the environment default
+    got2 = stage2.pair_stats(_device_stack(levels), P, nlevels, lo, hi, 0, sparse=True).host()
+    _check(got2, want)
