@@ -137,7 +137,7 @@ def by_line(tag):
     subprocess.run(["cuobjdump", "-xelf", "all", LIB], cwd=tmp, capture_output=True)
     # (kernel, the mangled fragment that names the captured instantiation in the cubin, source file)
     for kernel, mangled, src in (("mdmat_tile_kernel", "mdmat_tile_kernelILb0ELi256ELi2E", "mdmat"),
-                                 ("pair_stats_kernel", "pair_stats_kernelILb0E", "pair_stats"),
+                                 ("pair_stats_kernel", "pair_stats_kernelILb0ELb0E", "pair_stats"),
                                  ("xtc_groups_kernel", "xtc_groups_kernel", "xtc_gpu"), ("xtc_walk_kernel", "xtc_walk_kernel", "xtc_gpu"),
                                  ("pearson_sums_kernel", "pearson_sums_kernelILi4E", "dense_prep"),
                                  ("gemm3x_pair_kernel", "gemm3x_pair_kernel", "gemm3x")):
