@@ -3,8 +3,10 @@
 // instead of 12 and the host cores are out of the stage-1 feed (`gmx mdmat -f`, conan.py:1437-1453).
 //
 // A frame's bit stream (public xdrfile xdr3dfcoord scheme) is a chain of variable-width codes, but the
-// widths depend only on the run flags between the codes, so a warp takes one frame: it walks the
-// flags (cheap, sequential), then decodes 32 groups of atoms at a time in parallel, one per lane.
+// widths depend only on the run flags between the codes.  Two decoders: in one pass a warp takes one
+// frame, walks the flags together (sequential) and decodes 32 groups of atoms at a time, one per lane
+// (xtc_decode_kernel); in two passes one thread per frame walks the flags and writes a descriptor per
+// group, then one thread per group decodes (xtc_walk_kernel, xtc_groups_kernel; needs scratch memory).
 // Streams are read as aligned big-endian 32-bit words (XDR pads every frame to 4 bytes); only the
 // atoms of the index group are written.  The arithmetic is the integer arithmetic of the host decoder
 // in xtc.cpp, so the coordinates are bit-identical.
@@ -37,18 +39,13 @@ __device__ __forceinline__ uint32_t load_be32(const uint8_t* p) {
 }
 
 // MSB-first bit stream over aligned 32-bit words, one word loaded ahead of its use so the load latency
-// sits off the decode chain; reads past `end` give zeros and are reported.
+// sits off the decode chain; reads past `end` give zeros (the walk reports a stream that is too short).
 struct BitStream {
     const uint8_t* p;      // address of the word after `next`
     const uint8_t* end;
     uint64_t window;       // the next bits, left-aligned
     uint32_t next;         // the word that follows the window
     int have;
-    __device__ __forceinline__ void init(const uint8_t* begin, const uint8_t* e) {
-        p = begin; end = e; window = 0; have = 0;
-        next = (p < end) ? load_be32(p) : 0u;
-        p += 4;
-    }
     // start at bit `pos` of the stream that begins at `begin`
     __device__ __forceinline__ void init_at(const uint8_t* begin, const uint8_t* e, int64_t pos) {
         end = e;
@@ -72,10 +69,6 @@ struct BitStream {
         window <<= nbits;
         have -= nbits;
         return v;
-    }
-    // true if bits beyond the end of the stream were consumed
-    __device__ __forceinline__ bool past_end() const {
-        return p - ((have + 32) >> 3) > end;   // p minus the whole unread bytes (window + `next`)
     }
 };
 
