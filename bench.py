@@ -375,15 +375,18 @@ def run_ours(args):
     h_offs = [torch.from_numpy(XtcFile(b.tobytes()).offsets.copy()).pin_memory() for b in streams]
     del streams
     max_bytes = max(t.numel() for t in h_bytes)
-    NBUF = 4                     # staging buffers: the copies may run three batches ahead of the kernels
+    # staging buffers and decoder scratch for two steps' worth of batches: the bytes of a step travel, and the run
+    # flags of its frames are walked, while the step before is still computing
+    NBUF = 2 * nb
     stage_buf = [torch.empty(max_bytes, dtype=torch.uint8, device=dev) for _ in range(NBUF)]
     stage_off = [torch.empty(batch, dtype=torch.int64, device=dev) for _ in range(NBUF)]
+    dec_works = [torch.empty(int(lib.conan_xtc_decode_workspace_bytes(edges[b % nb + 1] - edges[b % nb], geom.natoms)),
+                             dtype=torch.uint8, device=dev) for b in range(NBUF)]
     d_coords = [torch.empty((batch, geom.natoms, 3), dtype=torch.float32, device=dev) for _ in range(2)]
     d_status = torch.zeros(nf, dtype=torch.int32, device=dev)
     work_b = torch.empty(stage1.mdmat_workspace_bytes(batch, geom), dtype=torch.uint8, device=dev)
-    # scratch of the two-pass decoder (one buffer: the decodes follow each other on one stream)
-    dec_work = torch.empty(int(lib.conan_xtc_decode_workspace_bytes(batch, geom.natoms)), dtype=torch.uint8, device=dev)
     copy_stream, dec_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev, priority=-1)
+    walk_stream = torch.cuda.Stream(dev, priority=-1)
     d2h_stream = torch.cuda.Stream(dev)
     host_out = {n: torch.empty(getattr(out, n).shape, dtype=getattr(out, n).dtype).pin_memory()
                 for n, _ in stage2.PairStats.PAIR_FIELDS + stage2.PairStats.FRAME_FIELDS}
@@ -391,30 +394,59 @@ def run_ours(args):
     h2d_bytes = sum(t.numel() for t in h_bytes) + sum(t.numel() * 8 for t in h_offs)
     float_bytes = h_xyz.numel() * 4
 
-    # three streams: copies run up to three batches ahead, the decoder (one warp per frame, far from filling
-    # the GPU) runs beside the distance kernel of the batch before it
+    # streams: copies and walks run a step ahead, the decode of a batch's groups just ahead of its distance kernel
     bytes_free = [None] * NBUF   # event after the decode that read each staging buffer (also across steps)
     coords_free = [None, None]   # event after the stage-1 launch that read each coordinate buffer
 
+    # timing experiments only (CONAN_BENCH_E2E_SKIP=copy,decode): leave parts of the feed out to see what they cost
+    skip = []          # (filled in after the warm-up steps, which always run the whole feed)
+
+    # The decoder's first pass (the walk over the run flags: one thread per frame, a millisecond of latency however
+    # many frames, few warps) needs only the bytes, so the walks of a step's batches are started when the LAST distance
+    # kernel of the step before has finished, i.e. beside its stage-2 kernel, which leaves room for them on every SM;
+    # beside the distance kernel (which holds all registers) every walk CTA would keep one of its CTAs out.  The second
+    # pass (one thread per group of atoms) runs per batch, just ahead of the batch's distance kernel.
+    distances_done = [None]      # event behind the last distance kernel of the step before
+    step_no = [0]
+
     def step_e2e():
+        base = (step_no[0] % 2) * nb
+        step_no[0] += 1
+        walked = []
         for b in range(nb):
             b0, b1 = edges[b], edges[b + 1]
-            k, c = b % NBUF, b % 2
+            k = base + b
             with torch.cuda.stream(copy_stream):
                 if bytes_free[k] is not None:
                     copy_stream.wait_event(bytes_free[k])
-                stage_buf[k][: h_bytes[b].numel()].copy_(h_bytes[b], non_blocking=True)
-                stage_off[k][: b1 - b0].copy_(h_offs[b], non_blocking=True)
+                if "copy" not in skip:
+                    stage_buf[k][: h_bytes[b].numel()].copy_(h_bytes[b], non_blocking=True)
+                    stage_off[k][: b1 - b0].copy_(h_offs[b], non_blocking=True)
                 copied = torch.cuda.Event()
                 copied.record(copy_stream)
+            with torch.cuda.stream(walk_stream):
+                walk_stream.wait_event(copied)
+                if distances_done[0] is not None:
+                    walk_stream.wait_event(distances_done[0])
+                if "decode" not in skip:
+                    _lib.check(lib.conan_xtc_walk_device(stage_buf[k].data_ptr(), h_bytes[b].numel(), stage_off[k].data_ptr(), b1 - b0,
+                                                         geom.natoms, None, geom.natoms, d_coords[b % 2].data_ptr(),
+                                                         d_status[b0:b1].data_ptr(), dec_works[k].data_ptr(), dec_works[k].numel(),
+                                                         walk_stream.cuda_stream))
+                ev = torch.cuda.Event()
+                ev.record(walk_stream)
+                walked.append(ev)
+        for b in range(nb):
+            b0, b1 = edges[b], edges[b + 1]
+            k, c = base + b, b % 2
             with torch.cuda.stream(dec_stream):
-                dec_stream.wait_event(copied)
+                dec_stream.wait_event(walked[b])
                 if coords_free[c] is not None:
                     dec_stream.wait_event(coords_free[c])
-                _lib.check(lib.conan_xtc_decode_device_ws(stage_buf[k].data_ptr(), h_bytes[b].numel(), stage_off[k].data_ptr(), b1 - b0,
-                                                          geom.natoms, None, geom.natoms, d_coords[c].data_ptr(),
-                                                          d_status[b0:b1].data_ptr(), dec_work.data_ptr(), dec_work.numel(),
-                                                          dec_stream.cuda_stream))
+                if "decode" not in skip:
+                    _lib.check(lib.conan_xtc_groups_device(stage_buf[k].data_ptr(), h_bytes[b].numel(), b1 - b0, geom.natoms, None,
+                                                           geom.natoms, d_coords[c].data_ptr(), dec_works[k].data_ptr(),
+                                                           dec_works[k].numel(), dec_stream.cuda_stream))
                 decoded = torch.cuda.Event()
                 decoded.record(dec_stream)
             bytes_free[k] = decoded
@@ -423,6 +455,7 @@ def run_ours(args):
             done = torch.cuda.Event()
             done.record(stream)
             coords_free[c] = done
+        distances_done[0] = coords_free[(nb - 1) % 2]
         if results_home[0] is not None:
             stream.wait_event(results_home[0])      # the previous step's results have left `out`
         if world > 1:
@@ -447,6 +480,7 @@ def run_ours(args):
         step_e2e()
     barrier()
     assert int(d_status.abs().sum().item()) == 0, "the GPU decoder rejected a frame of its own encoder's stream"
+    skip[:] = [w for w in os.environ.get("CONAN_BENCH_E2E_SKIP", "").split(",") if w]
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record(stream)
     for _ in range(args.steps):

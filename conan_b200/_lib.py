@@ -51,6 +51,10 @@ SIGNATURES = {
     "conan_xtc_decode_workspace_bytes": (ctypes.c_size_t, [c_i64, c_i32]),
     "conan_xtc_decode_device_ws": (ctypes.c_int, [c_void_p, c_i64, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_void_p,
                                                   c_void_p, c_void_p, ctypes.c_size_t, c_void_p]),
+    "conan_xtc_walk_device": (ctypes.c_int, [c_void_p, c_i64, c_void_p, c_i64, c_i32, c_void_p, c_i32, c_void_p,
+                                             c_void_p, c_void_p, ctypes.c_size_t, c_void_p]),
+    "conan_xtc_groups_device": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i32, c_void_p, c_i32, c_void_p,
+                                               c_void_p, ctypes.c_size_t, c_void_p]),
     "conan_write_matrices": (ctypes.c_int, [c_void_p, c_i64, c_i64, c_i64, c_i32, c_i32, c_i32, c_i32, c_i32,
                                             c_void_p, c_i32, c_i32, c_void_p, c_void_p, ctypes.c_char_p, c_i32]),
     "conan_write_pair_table": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_char_p, c_i32, c_i32, c_i32, c_i32, c_void_p, c_i32,

@@ -362,8 +362,9 @@ struct WalkParams {
 };
 
 constexpr int kWalkWindow = 256;        // words of every frame's stream held in shared memory by the walk
-constexpr int kWalkWarps = 3;           // warps (of 32 frames) per CTA: few, fat CTAs, because a walk CTA that lands on an SM
-                                        // beside the distance kernel keeps one of that kernel's two CTAs out while it runs
+constexpr int kWalkWarps = 2;           // warps (of 32 frames) per CTA: 66 KB of windows, which fit beside the two resident CTAs
+                                        // of the stage-2 kernel (a pipeline runs the walk of the next shard there); beside the
+                                        // distance kernel, whose CTAs hold all registers, a walk CTA keeps one of them out
 constexpr int kWalkSteps = 4;           // groups per round of the walk
 // words a lane may advance in one round before its reads leave the window: a group is at most 96 + 6 + 10 x 72 bits
 constexpr int kWalkMargin = ((kWalkSteps - 1) * (96 + 6 + 10 * 72) + 31) / 32 + 2;
@@ -543,6 +544,16 @@ __device__ __forceinline__ uint64_t peek64(const uint32_t* __restrict__ words, u
     return ((uint64_t)__funnelshift_l(b, a, sh) << 32) | __funnelshift_l(c, b, sh);
 }
 
+// the same from three words that are already here (a = the word that holds bit `pos`), and one bit of the 96
+__device__ __forceinline__ uint64_t peek64_words(uint32_t a, uint32_t b, uint32_t c, uint32_t pos) {
+    const int sh = (int)(pos & 31);
+    return ((uint64_t)__funnelshift_l(b, a, sh) << 32) | __funnelshift_l(c, b, sh);
+}
+__device__ __forceinline__ uint32_t bit_of_words(uint32_t a, uint32_t b, uint32_t c, uint32_t idx) {   // idx < 96
+    const uint32_t w = idx < 32 ? a : (idx < 64 ? b : c);
+    return (w >> (31 - (idx & 31))) & 1u;
+}
+
 // xdrfile's receiveints layout: of the nbits (1..64, here the top bits of X) the first `full` whole bytes are the
 // value's low bytes, least significant first, the last `part` (1..8) bits its top
 __device__ __forceinline__ uint64_t packed_value(uint64_t X, int nbits, int full, int part) {
@@ -580,11 +591,13 @@ __global__ void __launch_bounds__(kGroupThreads) xtc_groups_kernel(const WalkPar
     const int32_t* slot = prm.slot;
     const uint2* desc = wp.desc + (size_t)f * natoms;
     auto emit = [&](int atom, int32_t c0, int32_t c1, int32_t c2) {
-        const int s = slot ? slot[atom] : atom;
-        if (s >= 0 && s < prm.nsel) {
-            float* o = out + 3 * (size_t)s;
-            o[0] = (float)c0 * inv; o[1] = (float)c1 * inv; o[2] = (float)c2 * inv;
+        int s = atom;                  // without a slot map nsel == natoms and every atom has its row
+        if (slot) {
+            s = slot[atom];
+            if (s < 0 || s >= prm.nsel) return;
         }
+        float* o = out + 3u * (uint32_t)s;      // (at most 2^21 atoms per frame)
+        o[0] = (float)c0 * inv; o[1] = (float)c1 * inv; o[2] = (float)c2 * inv;
     };
     // Groups with small codes behind the full-size one are rare and long (a dependent chain of up to ten
     // codes), so they are not decoded where they are met: the lane parks them in a queue of its warp, and
@@ -645,19 +658,50 @@ __global__ void __launch_bounds__(kGroupThreads) xtc_groups_kernel(const WalkPar
         }
     };
 
-    for (int gb = g0; gb < g1; gb += kGroupThreads) {      // whole warps stay in the loop: the queue is theirs
+    // The descriptors of the thread's groups and the three stream words behind each are fetched up front, all
+    // loads in flight together (a descriptor and then its words are two dependent trips to memory; taken one group
+    // at a time they were a quarter of the kernel's stall samples), and parked in shared memory for the loop below.
+    constexpr int kIters = kGroupsPerCta / kGroupThreads;
+    __shared__ uint32_t st_pos[kIters][kGroupThreads], st_meta[kIters][kGroupThreads];
+    __shared__ uint32_t st_a[kIters][kGroupThreads], st_b[kIters][kGroupThreads], st_c[kIters][kGroupThreads];
+    {
+        uint2 d[kIters];
+#pragma unroll
+        for (int it = 0; it < kIters; it++) {
+            const int g = g0 + it * kGroupThreads + (int)threadIdx.x;
+            d[it] = g < g1 ? desc[g] : make_uint2(0u, 0u);
+        }
+        uint32_t wa[kIters], wb[kIters], wc[kIters];
+#pragma unroll
+        for (int it = 0; it < kIters; it++) {
+            const uint32_t w = d[it].x >> 5;
+            wa[it] = w < nwords ? __ldg(words + w) : 0u;
+            wb[it] = w + 1 < nwords ? __ldg(words + w + 1) : 0u;
+            wc[it] = w + 2 < nwords ? __ldg(words + w + 2) : 0u;
+        }
+#pragma unroll
+        for (int it = 0; it < kIters; it++) {
+            st_pos[it][threadIdx.x] = d[it].x; st_meta[it][threadIdx.x] = d[it].y;
+            st_a[it][threadIdx.x] = __byte_perm(wa[it], 0, 0x0123);
+            st_b[it][threadIdx.x] = __byte_perm(wb[it], 0, 0x0123);
+            st_c[it][threadIdx.x] = __byte_perm(wc[it], 0, 0x0123);
+        }
+        // (every thread reads back only what it wrote itself: no barrier)
+    }
+
+    for (int gb = g0, it = 0; gb < g1; gb += kGroupThreads, it++) {      // whole warps stay in the loop: the queue is theirs
         const int g = gb + (int)threadIdx.x;
         bool park = false;
         uint32_t sp = 0, meta = 0;
         int32_t cur[3] = {0, 0, 0};
         if (g < g1) {
-            const uint2 dsc = desc[g];
-            const uint32_t pos = dsc.x;
-            meta = dsc.y;
+            const uint32_t pos = st_pos[it][threadIdx.x];
+            meta = st_meta[it][threadIdx.x];
+            const uint32_t wa = st_a[it][threadIdx.x], wb = st_b[it][threadIdx.x], wc = st_c[it][threadIdx.x];
             const int my_first = (int)(meta & 0x1fffffu), my_ns = (int)((meta >> 21) & 15u);
             if (big_fast) {
                 // value = (c0 * s1 + c1) * s2 + c2
-                const uint64_t v = packed_value(peek64(words, nwords, pos), bitsize, bfull, bpart);
+                const uint64_t v = packed_value(peek64_words(wa, wb, wc, pos), bitsize, bfull, bpart);
                 uint32_t r2, r1;
                 const uint64_t qq = divmod64(v, sizeint[2], rcp2, r2);
                 const uint64_t q2 = divmod64(qq, sizeint[1], rcp1, r1);
@@ -679,9 +723,15 @@ __global__ void __launch_bounds__(kGroupThreads) xtc_groups_kernel(const WalkPar
                 // the flag behind the full-size code, five run bits if it is set, then the small codes
                 park = true;
                 sp = pos + (uint32_t)bigbits;
-                const uint32_t w = sp >> 5;
-                const uint32_t fw = w < nwords ? __byte_perm(__ldg(words + w), 0, 0x0123) : 0u;
-                sp += ((fw >> (31 - (sp & 31))) & 1u) ? 6u : 1u;
+                uint32_t flag;
+                if ((pos & 31u) + (uint32_t)bigbits < 96u) {
+                    flag = bit_of_words(wa, wb, wc, (pos & 31u) + (uint32_t)bigbits);
+                } else {      // (full-size codes of more than 64 bits)
+                    const uint32_t w = sp >> 5;
+                    const uint32_t fw = w < nwords ? __byte_perm(__ldg(words + w), 0, 0x0123) : 0u;
+                    flag = (fw >> (31 - (sp & 31))) & 1u;
+                }
+                sp += flag ? 6u : 1u;
             }
         }
         const unsigned parked = __ballot_sync(0xffffffffu, park);
@@ -722,6 +772,53 @@ extern "C" int conan_xtc_decode_device(const uint8_t* d_data, int64_t nbytes, co
     return CONAN_OK;
 }
 
+namespace {
+
+int walk_setup() {
+    // the walk's windows need more than the default 48 KB of shared memory: once per device
+    static std::atomic<uint64_t> configured{0};
+    int dev = 0;
+    CONAN_CUDA_TRY(cudaGetDevice(&dev));
+    const uint64_t bit = 1ull << (dev & 63);
+    if (!(configured.load(std::memory_order_acquire) & bit)) {
+        CONAN_CUDA_TRY(cudaFuncSetAttribute(xtc_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWalkSmem));
+        configured.fetch_or(bit, std::memory_order_release);
+    }
+    return CONAN_OK;
+}
+
+// pass 1 over n frames whose records / descriptors start at `rec` / `desc`
+int launch_walk(const DecodeParams& d, FrameRec* rec, uint2* desc, cudaStream_t st) {
+    WalkParams wp;
+    wp.d = d; wp.rec = rec; wp.desc = desc;
+    const int per = 32 * kWalkWarps;
+    xtc_walk_kernel<<<(unsigned)((d.nframes + per - 1) / per), per, kWalkSmem, st>>>(wp);
+    CONAN_CUDA_TRY(cudaGetLastError());
+    return CONAN_OK;
+}
+
+// pass 2 over the same n frames
+int launch_groups(const DecodeParams& d, FrameRec* rec, uint2* desc, cudaStream_t st) {
+    if (d.natoms <= 9) return CONAN_OK;        // frames of plain floats were written by pass 1
+    for (int64_t f0 = 0; f0 < d.nframes; f0 += 65535) {
+        const int64_t n = std::min<int64_t>(65535, d.nframes - f0);
+        WalkParams wp;
+        wp.d = d;
+        wp.d.offsets = d.offsets ? d.offsets + f0 : nullptr;
+        wp.d.nframes = n;
+        wp.d.xyz = d.xyz + (size_t)f0 * d.nsel * 3;
+        wp.d.status = d.status ? d.status + f0 : nullptr;
+        wp.rec = rec + f0;
+        wp.desc = desc + (size_t)f0 * d.natoms;
+        const dim3 grid((unsigned)((d.natoms + kGroupsPerCta - 1) / kGroupsPerCta), (unsigned)n);
+        xtc_groups_kernel<<<grid, kGroupThreads, 0, st>>>(wp);
+        CONAN_CUDA_TRY(cudaGetLastError());
+    }
+    return CONAN_OK;
+}
+
+}  // namespace
+
 extern "C" size_t conan_xtc_decode_workspace_bytes(int64_t nframes, int32_t natoms) {
     if (nframes <= 0 || natoms <= 0) return 0;
     return (size_t)nframes * (sizeof(FrameRec) + (size_t)natoms * sizeof(uint2));
@@ -745,33 +842,63 @@ extern "C" int conan_xtc_decode_device_ws(const uint8_t* d_data, int64_t nbytes,
         return conan::fail(CONAN_ERR_ARG, "conan_xtc_decode_device_ws: the workspace must be 16-byte aligned and hold at "
                                           "least one frame (%zu bytes)", per_frame);
     // as many frames per pass as the workspace holds (records first, descriptors behind them)
-    const int64_t chunk = (int64_t)std::min<size_t>((size_t)nframes, std::min<size_t>(work_bytes / per_frame, 65535));
+    const int64_t chunk = (int64_t)std::min<size_t>((size_t)nframes, work_bytes / per_frame);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    {
-        // the walk's windows need more than the default 48 KB of shared memory: once per device
-        static std::atomic<uint64_t> configured{0};
-        int dev = 0;
-        CONAN_CUDA_TRY(cudaGetDevice(&dev));
-        const uint64_t bit = 1ull << (dev & 63);
-        if (!(configured.load(std::memory_order_acquire) & bit)) {
-            CONAN_CUDA_TRY(cudaFuncSetAttribute(xtc_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWalkSmem));
-            configured.fetch_or(bit, std::memory_order_release);
-        }
-    }
+    int rc = walk_setup();
+    if (rc != CONAN_OK) return rc;
+    FrameRec* rec = static_cast<FrameRec*>(d_work);
+    uint2* desc = reinterpret_cast<uint2*>(static_cast<unsigned char*>(d_work) + (size_t)chunk * sizeof(FrameRec));
     for (int64_t f0 = 0; f0 < nframes; f0 += chunk) {
         const int64_t n = std::min(chunk, nframes - f0);
-        WalkParams wp;
-        wp.d = DecodeParams{d_data, nbytes, d_offsets + f0, n, natoms, d_slot, nsel, d_xyz + (size_t)f0 * nsel * 3,
-                            d_status + f0};
-        wp.rec = static_cast<FrameRec*>(d_work);
-        wp.desc = reinterpret_cast<uint2*>(static_cast<unsigned char*>(d_work) + (size_t)chunk * sizeof(FrameRec));
-        xtc_walk_kernel<<<(unsigned)((n + 32 * kWalkWarps - 1) / (32 * kWalkWarps)), 32 * kWalkWarps, kWalkSmem, st>>>(wp);
-        CONAN_CUDA_TRY(cudaGetLastError());
-        if (natoms > 9) {
-            const dim3 grid((unsigned)((natoms + kGroupsPerCta - 1) / kGroupsPerCta), (unsigned)n);
-            xtc_groups_kernel<<<grid, kGroupThreads, 0, st>>>(wp);
-            CONAN_CUDA_TRY(cudaGetLastError());
-        }
+        const DecodeParams d{d_data, nbytes, d_offsets + f0, n, natoms, d_slot, nsel, d_xyz + (size_t)f0 * nsel * 3, d_status + f0};
+        if ((rc = launch_walk(d, rec, desc, st)) != CONAN_OK) return rc;
+        if ((rc = launch_groups(d, rec, desc, st)) != CONAN_OK) return rc;
     }
     return CONAN_OK;
+}
+
+// The two passes as separate calls, for a pipeline that runs the walk of a batch early (it only needs the bytes, and
+// it is a latency-bound kernel of few warps that fits beside other kernels) and the decode when the coordinate buffer
+// is free.  The workspace must hold all nframes (conan_xtc_decode_workspace_bytes) and stay untouched in between.
+extern "C" int conan_xtc_walk_device(const uint8_t* d_data, int64_t nbytes, const int64_t* d_offsets, int64_t nframes,
+                                     int32_t natoms, const int32_t* d_slot, int32_t nsel, float* d_xyz,
+                                     int32_t* d_status, void* d_work, size_t work_bytes, void* stream) {
+    if (!d_data || !d_offsets || !d_xyz || !d_status || nbytes < 0 || nframes < 0 || natoms <= 0 || nsel < 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_walk_device: bad arguments");
+    if ((reinterpret_cast<uintptr_t>(d_data) & 3) != 0)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_walk_device: d_data must be 4-byte aligned");
+    if (!d_slot && nsel != natoms)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_walk_device: without a slot map nsel must equal natoms");
+    if (natoms > kMaxWsAtoms)
+        return conan::fail(CONAN_ERR_SIZE, "conan_xtc_walk_device: %d atoms per frame; the two-pass decoder takes up to %d "
+                                           "(use conan_xtc_decode_device)", natoms, kMaxWsAtoms);
+    if (nframes == 0) return CONAN_OK;
+    const size_t per_frame = sizeof(FrameRec) + (size_t)natoms * sizeof(uint2);
+    if (!d_work || (reinterpret_cast<uintptr_t>(d_work) & 15) != 0 || work_bytes / per_frame < (size_t)nframes)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_walk_device: the workspace must be 16-byte aligned and hold all %lld "
+                                          "frames (%zu bytes each)", (long long)nframes, per_frame);
+    int rc = walk_setup();
+    if (rc != CONAN_OK) return rc;
+    const DecodeParams d{d_data, nbytes, d_offsets, nframes, natoms, d_slot, nsel, d_xyz, d_status};
+    return launch_walk(d, static_cast<FrameRec*>(d_work),
+                       reinterpret_cast<uint2*>(static_cast<unsigned char*>(d_work) + (size_t)nframes * sizeof(FrameRec)),
+                       static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int conan_xtc_groups_device(const uint8_t* d_data, int64_t nbytes, int64_t nframes, int32_t natoms,
+                                       const int32_t* d_slot, int32_t nsel, float* d_xyz, const void* d_work,
+                                       size_t work_bytes, void* stream) {
+    if (!d_data || !d_xyz || nbytes < 0 || nframes < 0 || natoms <= 0 || nsel < 0 || natoms > kMaxWsAtoms)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_groups_device: bad arguments");
+    if (!d_slot && nsel != natoms)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_groups_device: without a slot map nsel must equal natoms");
+    if (nframes == 0) return CONAN_OK;
+    const size_t per_frame = sizeof(FrameRec) + (size_t)natoms * sizeof(uint2);
+    if (!d_work || (reinterpret_cast<uintptr_t>(d_work) & 15) != 0 || work_bytes / per_frame < (size_t)nframes)
+        return conan::fail(CONAN_ERR_ARG, "conan_xtc_groups_device: the workspace of the walk over the same %lld frames is "
+                                          "expected", (long long)nframes);
+    unsigned char* w = static_cast<unsigned char*>(const_cast<void*>(d_work));
+    const DecodeParams d{d_data, nbytes, nullptr, nframes, natoms, d_slot, nsel, d_xyz, nullptr};
+    return launch_groups(d, reinterpret_cast<FrameRec*>(w), reinterpret_cast<uint2*>(w + (size_t)nframes * sizeof(FrameRec)),
+                         static_cast<cudaStream_t>(stream));
 }

@@ -104,6 +104,18 @@ int conan_xtc_decode_device_ws(const uint8_t* d_data, int64_t nbytes, const int6
                                int32_t natoms, const int32_t* d_slot, int32_t nsel, float* d_xyz,
                                int32_t* d_status, void* d_work, size_t work_bytes, void* stream);
 
+/* The two passes as separate calls, for a pipeline that runs the walk of a batch early -- it needs only the bytes,
+ * and it is a latency-bound kernel of few warps that fits beside other kernels (bench.py runs it beside stage 2 of
+ * the shard before) -- and the decode of the groups when the coordinate buffer is free.  Arguments as above; the
+ * workspace must hold all nframes (conan_xtc_decode_workspace_bytes) and stay untouched between the two calls;
+ * d_status is written by the walk.  Systems of more than 2^21 atoms are refused here (CONAN_ERR_SIZE). */
+int conan_xtc_walk_device(const uint8_t* d_data, int64_t nbytes, const int64_t* d_offsets, int64_t nframes,
+                          int32_t natoms, const int32_t* d_slot, int32_t nsel, float* d_xyz, int32_t* d_status,
+                          void* d_work, size_t work_bytes, void* stream);
+int conan_xtc_groups_device(const uint8_t* d_data, int64_t nbytes, int64_t nframes, int32_t natoms,
+                            const int32_t* d_slot, int32_t nsel, float* d_xyz, const void* d_work,
+                            size_t work_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------ */
 /* Stage 1: per-frame residue-residue minimum-distance matrix, quantised to xpm levels.  */
 /* Replaces `gmx mdmat -frames` as invoked by conan.py:1437-1453 (:1783-1784) and the    */

@@ -116,3 +116,36 @@ def test_random_systems(torch_cuda, tmp_path):
         write_xtc(p, xyz, precision=precision)
         x = XtcFile(p)
         assert np.array_equal(x.decode_device().cpu().numpy(), x.decode()), (case, natoms, nframes, spread, cluster, precision)
+
+
+def test_walk_and_groups_as_separate_calls(torch_cuda, tmp_path):
+    """conan_xtc_walk_device + conan_xtc_groups_device (the two passes apart, as a pipeline runs them) give what the
+    one call gives; a workspace that cannot hold all frames is refused."""
+    import torch
+    from conan_b200 import _lib, synth
+    from conan_b200.xtc import XtcFile, write_xtc
+    lib = _lib.load()
+    xyz, _, L = synth.make_trajectory(120, 90, seed=9)
+    p = str(tmp_path / "w.xtc")
+    write_xtc(p, xyz)
+    x = XtcFile(p)
+    want = x.decode()
+    dev = torch.device("cuda")
+    d_data = torch.from_numpy(np.array(x._buf)).to(dev)
+    d_off = torch.from_numpy(x.offsets).to(dev)
+    nf, na = x.nframes, x.natoms
+    need = int(lib.conan_xtc_decode_workspace_bytes(nf, na))
+    d_work = torch.empty(need, dtype=torch.uint8, device=dev)
+    out = torch.zeros((nf, na, 3), dtype=torch.float32, device=dev)
+    status = torch.full((nf,), -1, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    _lib.check(lib.conan_xtc_walk_device(d_data.data_ptr(), d_data.numel(), d_off.data_ptr(), nf, na, None, na, out.data_ptr(),
+                                         status.data_ptr(), d_work.data_ptr(), d_work.numel(), st))
+    torch.cuda.synchronize()
+    assert int(status.abs().sum().item()) == 0 and float(out.abs().sum().item()) == 0.0      # nothing decoded yet
+    _lib.check(lib.conan_xtc_groups_device(d_data.data_ptr(), d_data.numel(), nf, na, None, na, out.data_ptr(),
+                                           d_work.data_ptr(), d_work.numel(), st))
+    assert np.array_equal(out.cpu().numpy(), want)
+    with pytest.raises(_lib.ConanError):
+        _lib.check(lib.conan_xtc_walk_device(d_data.data_ptr(), d_data.numel(), d_off.data_ptr(), nf, na, None, na, out.data_ptr(),
+                                             status.data_ptr(), d_work.data_ptr(), need // 2, st))
