@@ -508,6 +508,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
     int* origI = rowbase + kTile;                       // [64] residue at row position i / column position j of the tile
     int* origJ = origI + kTile;
     float* boxs = reinterpret_cast<float*>(origJ + kTile);   // [kMaxFB][6] box lengths of the group's frames and their reciprocals
+    uint16_t** rowptr = reinterpret_cast<uint16_t**>(boxs + kMaxFB * 6);   // [kMaxFB] the group's frames in the level stack
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int t = (int)blockIdx.x;                                   // tile
@@ -545,6 +546,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
         fence_mbar_init();
         for (int c = 0; c < 5; c++) counters[c] = 0;
     }
+    if (tid < kMaxFB) rowptr[tid] = prm.levels + (size_t)(f0 + tid) * prm.stride;
     __syncthreads();
     if (prm.use_tma) {
         if (tid == 0) {
@@ -633,19 +635,33 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
             const int n = jhi - jlo;
             if (n <= 0) continue;
             uint16_t* p = prm.levels + (size_t)f0 * prm.stride + pair_idx(gi, gj0) + jlo;
+            // 16-byte aligned body, scalar head and tail (up to seven elements each); with a row pitch that is a
+            // multiple of eight elements the split is the same in every frame of the group
+            int mis = (int)((reinterpret_cast<uintptr_t>(p) >> 1) & 7);   // elements past alignment
+            int head = min((8 - mis) & 7, n);
+            int nq = (n - head) >> 3;
+            int tail0 = head + 8 * nq;
+            const bool same_split = (prm.stride & 7) == 0;
             for (int g = 0; g < nfb; g++, p += prm.stride) {
-                // 16-byte aligned body, scalar head and tail (up to seven elements each)
-                const int mis = (int)((reinterpret_cast<uintptr_t>(p) >> 1) & 7);   // elements past alignment
-                const int head = min((8 - mis) & 7, n);
-                const int nq = (n - head) >> 3;
+                if (!same_split && g > 0) {
+                    mis = (int)((reinterpret_cast<uintptr_t>(p) >> 1) & 7);
+                    head = min((8 - mis) & 7, n);
+                    nq = (n - head) >> 3;
+                    tail0 = head + 8 * nq;
+                }
                 if (l8 < head) p[l8] = ml;
                 if (l8 < nq) *reinterpret_cast<uint4*>(p + head + 8 * l8) = make_uint4(fillv, fillv, fillv, fillv);
-                const int tail0 = head + 8 * nq;
                 if (l8 < n - tail0) p[tail0 + l8] = ml;
             }
         }
     }
-    __syncthreads();   // spheres, counts and the fill are in place
+    // spheres, counts and the fill are in place; the same barrier tells whether every residue of both tile sides has
+    // exactly eight atoms (padding positions have none and never enter the list): their items then run a copy of the
+    // atom loop with the counts as constants
+    int mycnt = 8;                 // (threads 0..127 wrote the counts of their own positions above)
+    if (tid < kTile) mycnt = cntI[tid];
+    else if (tid < 2 * kTile) mycnt = cntJ[tid - kTile];
+    const bool full8 = __syncthreads_and(mycnt == 8 || mycnt == 0) != 0;
 
     bool tiles_ready = !prm.use_tma;
 
@@ -675,7 +691,10 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 if (!PBC || !(e & 0x1000)) {
                     const float* ri = aI + g * (kPlanesI * pstride) + i * kpad;
                     const float* rj = aJ + g * (kPlanesJ * pstride) + j * kpad;
-                    if (k8)
+                    if (k8 && full8)
+                        level = fast_pair<PBC, true>(prm, ri, rj, 8 * kTile, swz & i, swz & j, sphI[g * kTile + i],
+                                                     sphJ[g * kTile + j], 8, 8, PBC ? boxs + 6 * g : nullptr);
+                    else if (k8)
                         level = fast_pair<PBC, true>(prm, ri, rj, 8 * kTile, swz & i, swz & j, sphI[g * kTile + i],
                                                      sphJ[g * kTile + j], ci, cj, PBC ? boxs + 6 * g : nullptr);
                     else   // 64-byte swizzle (kpad == 16): the four 16-byte quarters of a residue's row are permuted by (row / 2) % 4
@@ -707,7 +726,7 @@ mdmat_tile_kernel(const __grid_constant__ CUtensorMap tmapI, const __grid_consta
                 if (lane == src) level = lv;
             }
             if (level < maxlevel)
-                prm.levels[(size_t)(f0 + g) * prm.stride + rowbase[i] + origJ[j]] = (uint16_t)level;
+                rowptr[g][rowbase[i] + origJ[j]] = (uint16_t)level;
         }
         __syncthreads();
     };
@@ -842,6 +861,7 @@ size_t mdmat_smem_bytes(int kpad, int fb) {
     s += (size_t)kListCap * sizeof(uint16_t);                   // survivor list
     s += 8 + 6 * sizeof(int) + 3 * kTile * sizeof(int);         // mbarrier + counters + row bases + residue numbers
     s += kMaxFB * 6 * sizeof(float);                            // box lengths of the group's frames and reciprocals
+    s += kMaxFB * sizeof(void*);                                // the group's rows of the level stack
     return (s + 15) & ~(size_t)15;
 }
 
