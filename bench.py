@@ -263,7 +263,10 @@ def run_ours(args):
             dist.destroy_process_group()
             raise SystemExit(1)
     # one long trajectory of nf * world frames (one seed); every rank takes its own consecutive frame range
-    xyz, res_start, _ = synth.make_trajectory(nres, nf * world, ATOMS_PER_RES, seed=4, frame_range=(rank * nf, (rank + 1) * nf))
+    # (the slow global modes of the synthetic system repeat every shard length, so every rank's shard holds the same
+    #  amount of work as the one-GPU run: weak scaling with fixed work per GPU)
+    xyz, res_start, _ = synth.make_trajectory(nres, nf * world, ATOMS_PER_RES, seed=4, frame_range=(rank * nf, (rank + 1) * nf),
+                                              mode_period=nf)
     geom = stage1.Geometry(res_start)
     P = geom.P
     lo, hi, eq = thresholds()
@@ -520,7 +523,7 @@ def run_ours(args):
                 "workload": "C4 shard: %d residues x %d frames per GPU (BASELINE configs[3] = 8 such shards)" % (nres, nf),
                 "nres": nres, "atoms_per_res": ATOMS_PER_RES, "pairs": P, "frames_per_gpu": nf,
                 "trunc": TRUNC, "nlevels": NLEVELS, "trunc_inter": TRUNC_INTER, "trunc_inter_high": TRUNC_INTER_HIGH,
-                "sharding": "frames x%d" % world,
+                "sharding": "frames x%d (consecutive ranges of one trajectory whose slow global modes repeat every %d frames)" % (world, nf),
                 "l2": "inputs larger than L2 (%.1f GB coordinates, %.1f GB levels per GPU); no flush needed"
                       % (float_bytes / 1e9, levels.numel() * 2 / 1e9),
             },

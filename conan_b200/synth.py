@@ -43,14 +43,16 @@ def _globule(rng, nres, density=7.0, bond=0.38, min_dist=0.30):
 
 
 def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtype=np.float32, closer=0.0,
-                    frame_range=None):
+                    frame_range=None, mode_period=None):
     """Returns (xyz [nframes, natoms, 3] float32 nm, res_start [nres+1] int32, box_length nm).
 
     two_chain=(nx, ny): two globules of nx and ny residues whose separation follows an OU process
     around 1.5 nm surface distance (the asymmetric interface configuration); closer (nm) moves the second
     globule towards the first, for small systems that should share more than a handful of contacts.
     frame_range=(f0, f1): only frames f0..f1-1 of the nframes-long trajectory are returned (a frame shard of
-    one long run: the random stream is advanced through the frames before it, nothing else is kept)."""
+    one long run: the random stream is advanced through the frames before it, nothing else is kept).
+    mode_period: the slow global modes (breathing, drift) repeat every mode_period frames instead of spanning the
+    whole run, so that equal frame shards of a long run hold the same amount of work (weak scaling); None = nframes."""
     rng = np.random.default_rng(seed)
     if two_chain is None:
         centres, R = _globule(rng, nres)
@@ -84,7 +86,10 @@ def make_trajectory(nres, nframes, atoms_per_res=8, seed=3, two_chain=None, dtyp
             if f_lo <= f0 + k < f_hi:
                 disp[f0 + k - f_lo] = state
     t = np.arange(f_lo, f_hi, dtype=np.float64)
-    breathing = 1.0 + 0.04 * np.sin(2.0 * np.pi * t / max(nframes / 3.0, 50.0)) + 0.02 * t / max(nframes, 1)
+    span = float(nframes if mode_period is None else mode_period)
+    if mode_period is not None:
+        t = np.mod(t, span)
+    breathing = 1.0 + 0.04 * np.sin(2.0 * np.pi * t / max(span / 3.0, 50.0)) + 0.02 * t / max(span, 1.0)
     cen = centres[None, :, :] * breathing[:, None, None] + disp
     if shift is not None:
         nx, ny = shift
